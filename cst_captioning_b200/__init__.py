@@ -1,0 +1,18 @@
+"""B200-native CIDEr-D reward path of CST captioning (one hot path, drop-in).
+
+Public surface (mirrors the reference's interfaces for this path):
+
+* :class:`CiderD`                      <- ``pyciderevalcap.ciderD.ciderD.CiderD``
+* :func:`get_cst_reward`               <- ``utils.get_cst_reward`` (``utils.py:229``)
+* :func:`get_self_critical_reward`     <- ``utils.get_self_critical_reward`` (``utils.py:169``)
+* :class:`DfTable`                     <- the ``*_ciderdf.pkl`` of ``compute_ciderdf.py``
+* :class:`RefSet`                      device-resident reference rows
+
+Importing this package loads ``libcst_reward.so`` (hand-written CUDA for
+sm_100a behind the C ABI of ``include/cst_reward.h``) and fails if it has not
+been built: there is no CPU fallback.
+"""
+from ._lib import CstError, LIB_PATH, lib          # noqa: F401  (loads the .so)
+from .df_table import DfTable, pack_ngrams, unpack_keys  # noqa: F401
+from .ciderd import CiderD                          # noqa: F401
+from .reward import RefSet, get_cst_reward, get_self_critical_reward  # noqa: F401

@@ -1,0 +1,199 @@
+// Shared device helpers of the CIDEr-D reward kernels (sm_100a).
+//
+// Data layout in HBM / shared memory is described in DESIGN.md; the packed key
+// format and the C ABI in include/cst_reward.h.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+#define CST_FULL 0xffffffffu
+#define CST_SIGMA 6.0          /* CiderD default sigma (train.py:121 builds CiderD with defaults) */
+#define CST_GAUSS_HALF 32      /* LUT covers length deltas in [-32, 32] */
+#define CST_GAUSS_N (2 * CST_GAUSS_HALF + 1)
+
+// ---------------------------------------------------------------------------
+// global df table: open addressing, linear probing, 16-byte slots so that one
+// LDG.128 fetches key and idf together.
+// ---------------------------------------------------------------------------
+struct __align__(16) DfSlot {
+    u64 key;      // 0 = empty
+    double idf;   // log(n_documents) - log(max(1, df)), computed by the caller in float64
+};
+
+// Fibonacci hash: bits 32..63 of key * phi.  Both tables (global df table,
+// per-video shared table) are indexed from this one value.
+__host__ __device__ __forceinline__ u32 cst_hash(u64 key) {
+    return (u32)((key * 0x9E3779B97F4A7C15ull) >> 32);
+}
+// Lemire range reduction, valid for any capacity < 2^32.
+__host__ __device__ __forceinline__ u32 cst_slot(u32 h, u32 cap) {
+    return (u32)(((u64)h * (u64)cap) >> 32);
+}
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ ulonglong2 ld_slot(const DfSlot* p) {
+    return __ldg(reinterpret_cast<const ulonglong2*>(p));
+}
+
+// idf of up to four keys per lane, first probes issued back to back so the four
+// L2 round trips overlap.  Lanes/orders with need[k] == false cost one load of
+// slot 0 (hot in L1) and get `unseen`.
+__device__ __forceinline__ void df_probe4(const DfSlot* __restrict__ tab, u32 cap, double unseen,
+                                          const u64 key[4], const u32 h[4], const bool need[4],
+                                          double idf[4]) {
+    u32 s[4];
+    ulonglong2 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        s[k] = need[k] ? cst_slot(h[k], cap) : 0u;
+        v[k] = ld_slot(tab + s[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        double r = unseen;
+        if (need[k]) {
+            ulonglong2 x = v[k];
+            u32 q = s[k];
+            for (;;) {
+                if (x.x == key[k]) { r = __longlong_as_double((long long)x.y); break; }
+                if (x.x == 0ull) break;
+                q = (q + 1 == cap) ? 0u : q + 1;
+                x = ld_slot(tab + q);
+            }
+        }
+        idf[k] = r;
+    }
+}
+
+__device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u; }
+
+// ---------------------------------------------------------------------------
+// Row canonicalisation + n-gram keys, one warp per row, lane = token position.
+// Restates utils.py:135-152 (array_to_str) and compute_ciderdf.py:28-33
+// (precook's k/i loops) on packed keys.
+//   key[k]   packed (k+1)-gram starting at this lane's position, 0 if none
+//   L        canonical token count (warp uniform)
+//   returns  true if the row held an id outside [-1, 65534] before its end
+// tokbuf: 32 u32 of warp-private shared memory.
+// ---------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, int use_eos,
+                                          int lane, u32* tokbuf, u64 key[4], int& L) {
+    const bool in = lane < width;
+    long long t = in ? (long long)row[lane] : 0ll;
+    const bool bad = in && (t < -1 || t > 65534);
+    const bool term = in && (t == 0 || t == -1 || bad);   // -1 = padding: ends the row, never emitted
+    const u32 tmask = __ballot_sync(CST_FULL, term);
+    const u32 bmask = __ballot_sync(CST_FULL, bad);
+    const int end = tmask ? (__ffs(tmask) - 1) : width;   // first <end> (or bad id), else row width
+    const u32 upto_end = (end >= 31) ? CST_FULL : ((2u << end) - 1u);
+    const bool keep = (lane < end && t != 1) || (use_eos && lane == end && in && t == 0);
+    const u32 kmask = __ballot_sync(CST_FULL, keep);
+    L = __popc(kmask);
+    const int pos = __popc(kmask & lanemask_lt(lane));
+    if (keep) tokbuf[pos] = (u32)t + 1u;
+    __syncwarp();
+    const u32 e0 = (lane < L) ? tokbuf[lane] : 0u;
+    __syncwarp();
+    u32 e1 = __shfl_down_sync(CST_FULL, e0, 1);
+    u32 e2 = __shfl_down_sync(CST_FULL, e0, 2);
+    u32 e3 = __shfl_down_sync(CST_FULL, e0, 3);
+    if (lane + 1 >= L) e1 = 0;
+    if (lane + 2 >= L) e2 = 0;
+    if (lane + 3 >= L) e3 = 0;
+    const u64 k1 = (u64)e0;
+    const u64 k2 = k1 | ((u64)e1 << 16);
+    const u64 k3 = k2 | ((u64)e2 << 32);
+    const u64 k4 = k3 | ((u64)e3 << 48);
+    key[0] = k1;
+    key[1] = e1 ? k2 : 0ull;
+    key[2] = e2 ? k3 : 0ull;
+    key[3] = e3 ? k4 : 0ull;
+    return (bmask & upto_end) != 0u;
+}
+
+// Term frequency of each lane's n-gram inside its own row via MATCH.ANY; the
+// lowest lane of every group of equal keys is the group's leader (the dict entry
+// precook would create at that position).
+__device__ __forceinline__ void row_tf(const u64 key[4], int lane, int tf[4], bool lead[4]) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const u32 m = __match_any_sync(CST_FULL, key[k]);
+        tf[k] = __popc(m);
+        lead[k] = (key[k] != 0ull) && ((__ffs(m) - 1) == lane);
+    }
+}
+
+// Sum four per-lane doubles over the warp with a transposed butterfly: 6 exchanges
+// instead of 20.  On return every lane holds the warp total of ONE of the four
+// inputs: order o = 2 * bit4(lane) + bit3(lane).
+__device__ __forceinline__ double warp_sum4_transposed(const double v[4], int lane) {
+    const bool hi16 = (lane & 16) != 0;
+    const bool hi8 = (lane & 8) != 0;
+    // exchange with lane^16: low half keeps orders {0,1}, high half keeps {2,3}
+    double sendA = hi16 ? v[0] : v[2];
+    double sendB = hi16 ? v[1] : v[3];
+    double keepA = hi16 ? v[2] : v[0];
+    double keepB = hi16 ? v[3] : v[1];
+    keepA += __shfl_xor_sync(CST_FULL, sendA, 16);
+    keepB += __shfl_xor_sync(CST_FULL, sendB, 16);
+    // exchange with lane^8: bit3 == 0 keeps the first of the pair, bit3 == 1 the second
+    double send = hi8 ? keepA : keepB;
+    double x = hi8 ? keepB : keepA;
+    x += __shfl_xor_sync(CST_FULL, send, 8);
+    x += __shfl_xor_sync(CST_FULL, x, 4);
+    x += __shfl_xor_sync(CST_FULL, x, 2);
+    x += __shfl_xor_sync(CST_FULL, x, 1);
+    return x;
+}
+__device__ __forceinline__ int lane_order(int lane) { return ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1); }
+
+__device__ __forceinline__ double inv_norm_of(double sumsq) {
+    return sumsq > 0.0 ? 1.0 / sqrt(sumsq) : 0.0;
+}
+
+// ---------------------------------------------------------------------------
+// per-video shared-memory table: union of the n-grams of (up to 32) refs.
+//   key   packed n-gram, 0 = empty
+//   P     bit r set  <=>  ref r of the chunk contains the n-gram
+//   M     bit r set  <=>  ref r contains it more than once; the exact count then
+//         lives under the synthetic key count_key(slot, r) (field P)
+// ---------------------------------------------------------------------------
+struct __align__(16) VidSlot {
+    u64 key;
+    u32 P;
+    u32 M;
+};
+
+// Real keys always have a non-zero low 16-bit lane, synthetic ones a zero one.
+__device__ __forceinline__ u64 count_key(u32 slot, u32 r) {
+    return (1ull << 63) | ((u64)slot << 24) | ((u64)r << 16);
+}
+
+__device__ __forceinline__ u32 vid_insert(VidSlot* tab, u32 mask, u32 idx, u64 key) {
+    for (;;) {
+        u64 cur = *reinterpret_cast<volatile u64*>(&tab[idx].key);
+        if (cur == key) return idx;
+        if (cur == 0ull) {
+            u64 old = atomicCAS(reinterpret_cast<u64*>(&tab[idx].key), 0ull, key);
+            if (old == 0ull || old == key) return idx;
+        }
+        idx = (idx + 1) & mask;
+    }
+}
+
+__device__ __forceinline__ int vid_find(const VidSlot* tab, u32 mask, u32 idx, u64 key) {
+    for (;;) {
+        u64 cur = tab[idx].key;
+        if (cur == key) return (int)idx;
+        if (cur == 0ull) return -1;
+        idx = (idx + 1) & mask;
+    }
+}
+
+#endif  // __CUDACC__

@@ -1,0 +1,1053 @@
+// CIDEr-D reward path for B200 (sm_100a): kernels + C ABI (include/cst_reward.h).
+//
+// One CTA per video.  Phase R: one warp per reference caption canonicalises its
+// row, packs the 1..4-gram keys, fetches their idf from the L2-resident df table
+// and publishes "which refs contain this n-gram" into a shared-memory hash table
+// (the video's reference n-gram vectors, staged once and reused by every
+// candidate of the video).  Phase C: one warp per candidate does the same for its
+// row, walks the presence bits of the n-grams it shares with the refs and reduces
+// the clipped tf-idf cosine x Gaussian length penalty with warp shuffles.  Phase B:
+// the SCB / greedy baseline of utils.py:292-322 on the CTA's scores, reward write,
+// per-video statistics; the last CTA folds the statistics deterministically.
+//
+// No tensor cores: the work is sparse hashing, not a dense contraction.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "cst_common.cuh"
+#include "cst_reward.h"
+
+// ---------------------------------------------------------------------------
+// error plumbing
+// ---------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                 \
+    do {                                                                               \
+        cudaError_t e_ = (expr);                                                       \
+        if (e_ != cudaSuccess)                                                         \
+            return fail(CST_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));   \
+    } while (0)
+
+extern "C" const char* cst_last_error(void) { return g_err; }
+extern "C" int cst_abi_version(void) { return 1; }
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) return;
+        ok = (prev == dev) || (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+// ---------------------------------------------------------------------------
+// df table handle
+// ---------------------------------------------------------------------------
+struct cst_df_table {
+    int device;
+    u32 capacity;
+    int64_t size;
+    double idf_unseen;
+    DfSlot* slots;   // [capacity]  hot: key + idf, one LDG.128 per probe
+    double* df;      // [capacity]  cold: raw document frequency (parity probe / export)
+    double* gauss;   // [CST_GAUSS_N] e^{-d^2 / (2 sigma^2)}, d = index - CST_GAUSS_HALF
+};
+
+static u32 df_capacity_for(int64_t n) {
+    int64_t cap = 2 * n + 16;   // load factor <= 0.5
+    if (cap < 1024) cap = 1024;
+    return (u32)cap;
+}
+
+// Gaussian length penalty exactly as the scorer evaluates it:
+// np.e ** (-(delta ** 2) / (2 * sigma ** 2)) on Python floats, i.e. libm pow.
+static void fill_gauss(double* g) {
+    const double e = 2.718281828459045;
+    for (int i = 0; i < CST_GAUSS_N; ++i) {
+        double delta = (double)(i - CST_GAUSS_HALF);
+        g[i] = pow(e, -(delta * delta) / (2.0 * (CST_SIGMA * CST_SIGMA)));
+    }
+}
+
+static int table_alloc(int device, u32 cap, double idf_unseen, cst_df_table** out) {
+    cst_df_table* t = new (std::nothrow) cst_df_table();
+    if (!t) return fail(CST_E_NOMEM, "out of host memory");
+    t->device = device;
+    t->capacity = cap;
+    t->size = 0;
+    t->idf_unseen = idf_unseen;
+    t->slots = nullptr;
+    t->df = nullptr;
+    t->gauss = nullptr;
+    double g[CST_GAUSS_N];
+    fill_gauss(g);
+    cudaError_t e = cudaMalloc(&t->slots, (size_t)cap * sizeof(DfSlot));
+    if (e == cudaSuccess) e = cudaMalloc(&t->df, (size_t)cap * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&t->gauss, sizeof(g));
+    if (e == cudaSuccess) e = cudaMemcpy(t->gauss, g, sizeof(g), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(t->slots);
+        cudaFree(t->df);
+        cudaFree(t->gauss);
+        delete t;
+        return fail(e == cudaErrorMemoryAllocation ? CST_E_NOMEM : CST_E_CUDA, "df table allocation: %s",
+                    cudaGetErrorString(e));
+    }
+    *out = t;
+    return CST_OK;
+}
+
+extern "C" int cst_df_create(const uint64_t* keys, const double* df, const double* idf, int64_t n,
+                             double idf_unseen, int device, cst_df_table** out) {
+    if (!out) return fail(CST_E_ARG, "cst_df_create: out is NULL");
+    *out = nullptr;
+    if (n < 0 || (n > 0 && (!keys || !df || !idf))) return fail(CST_E_ARG, "cst_df_create: NULL input");
+    if (n > (int64_t)1 << 30) return fail(CST_E_RANGE, "cst_df_create: %lld n-grams exceed 2^30", (long long)n);
+    if (!(idf_unseen >= 0.0)) return fail(CST_E_ARG, "cst_df_create: idf_unseen must be >= 0");
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_df_create: cannot select CUDA device %d", device);
+
+    const u32 cap = df_capacity_for(n);
+    std::vector<DfSlot> h_slots;
+    std::vector<double> h_df;
+    try {
+        h_slots.assign(cap, DfSlot{0ull, 0.0});
+        h_df.assign(cap, 0.0);
+    } catch (const std::bad_alloc&) {
+        return fail(CST_E_NOMEM, "cst_df_create: out of host memory for %u slots", cap);
+    }
+    for (int64_t i = 0; i < n; ++i) {
+        const u64 k = keys[i];
+        if (k == 0ull || (k & 0xffffull) == 0ull)
+            return fail(CST_E_ARG, "cst_df_create: key %lld is not a packed n-gram", (long long)i);
+        if (!(idf[i] >= 0.0))
+            return fail(CST_E_ARG, "cst_df_create: idf[%lld] < 0 (df exceeds the document count)", (long long)i);
+        u32 s = cst_slot(cst_hash(k), cap);
+        while (h_slots[s].key != 0ull) {
+            if (h_slots[s].key == k) return fail(CST_E_ARG, "cst_df_create: duplicate key at %lld", (long long)i);
+            s = (s + 1 == cap) ? 0u : s + 1;
+        }
+        h_slots[s].key = k;
+        h_slots[s].idf = idf[i];
+        h_df[s] = df[i];
+    }
+    cst_df_table* t = nullptr;
+    int rc = table_alloc(device, cap, idf_unseen, &t);
+    if (rc != CST_OK) return rc;
+    cudaError_t e = cudaMemcpy(t->slots, h_slots.data(), (size_t)cap * sizeof(DfSlot), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(t->df, h_df.data(), (size_t)cap * sizeof(double), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cst_df_destroy(t);
+        return fail(CST_E_CUDA, "cst_df_create: upload failed: %s", cudaGetErrorString(e));
+    }
+    t->size = n;
+    *out = t;
+    return CST_OK;
+}
+
+extern "C" int cst_df_destroy(cst_df_table* t) {
+    if (!t) return CST_OK;
+    DeviceGuard guard(t->device);
+    cudaFree(t->slots);
+    cudaFree(t->df);
+    cudaFree(t->gauss);
+    delete t;
+    return CST_OK;
+}
+
+extern "C" int64_t cst_df_size(const cst_df_table* t) { return t ? t->size : -1; }
+extern "C" int64_t cst_df_capacity(const cst_df_table* t) { return t ? (int64_t)t->capacity : -1; }
+extern "C" int cst_df_device(const cst_df_table* t) { return t ? t->device : -1; }
+
+extern "C" int cst_df_export(const cst_df_table* t, uint64_t* keys_out, double* df_out) {
+    if (!t || (t->size > 0 && (!keys_out || !df_out))) return fail(CST_E_ARG, "cst_df_export: NULL argument");
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_df_export: cannot select device %d", t->device);
+    std::vector<DfSlot> h_slots(t->capacity);
+    std::vector<double> h_df(t->capacity);
+    CUDA_TRY(cudaMemcpy(h_slots.data(), t->slots, (size_t)t->capacity * sizeof(DfSlot), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(h_df.data(), t->df, (size_t)t->capacity * sizeof(double), cudaMemcpyDeviceToHost));
+    int64_t at = 0;
+    for (u32 s = 0; s < t->capacity; ++s) {
+        if (h_slots[s].key == 0ull) continue;
+        if (at >= t->size) return fail(CST_E_CUDA, "cst_df_export: table holds more keys than its size");
+        keys_out[at] = h_slots[s].key;
+        df_out[at] = h_df[s];
+        ++at;
+    }
+    if (at != t->size) return fail(CST_E_CUDA, "cst_df_export: found %lld keys, expected %lld", (long long)at, (long long)t->size);
+    return CST_OK;
+}
+
+// ---------------------------------------------------------------------------
+// parity probes
+// ---------------------------------------------------------------------------
+__global__ void k_df_lookup(const DfSlot* __restrict__ tab, const double* __restrict__ dfv, u32 cap,
+                            double unseen, const u64* __restrict__ keys, int64_t n, double* df_out,
+                            double* idf_out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u64 key = keys[i];
+    double d = 0.0, w = unseen;
+    if (key != 0ull) {
+        u32 s = cst_slot(cst_hash(key), cap);
+        for (;;) {
+            ulonglong2 x = ld_slot(tab + s);
+            if (x.x == key) { d = dfv[s]; w = __longlong_as_double((long long)x.y); break; }
+            if (x.x == 0ull) break;
+            s = (s + 1 == cap) ? 0u : s + 1;
+        }
+    }
+    df_out[i] = d;
+    if (idf_out) idf_out[i] = w;
+}
+
+extern "C" int cst_df_lookup(const cst_df_table* t, const uint64_t* keys, int64_t n, double* df_out,
+                             double* idf_out, void* stream) {
+    if (!t || n < 0 || (n > 0 && (!keys || !df_out))) return fail(CST_E_ARG, "cst_df_lookup: bad argument");
+    if (n == 0) return CST_OK;
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_df_lookup: cannot select device %d", t->device);
+    const int threads = 256;
+    const int64_t blocks = (n + threads - 1) / threads;
+    k_df_lookup<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(
+        t->slots, t->df, t->capacity, t->idf_unseen, (const u64*)keys, n, df_out, idf_out);
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+template <typename T>
+__global__ void k_ngram_counts(const T* __restrict__ rows, int64_t n_rows, int width, int64_t stride,
+                               int use_eos, u64* keys_out, int* counts_out, int* n_out, int* len_out) {
+    __shared__ u32 tokbuf[8][32];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int64_t row = (int64_t)blockIdx.x * 8 + warp;
+    if (row >= n_rows) return;
+    u64 key[4];
+    int L;
+    canon_row<T>(rows + row * stride, width, use_eos, lane, tokbuf[warp], key, L);
+    int tf[4];
+    bool lead[4];
+    row_tf(key, lane, tf, lead);
+    int base = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const u32 lm = __ballot_sync(CST_FULL, lead[k]);
+        if (lead[k]) {
+            const int at = base + __popc(lm & lanemask_lt(lane));
+            keys_out[row * CST_NGRAM_SLOTS_PER_ROW + at] = key[k];
+            counts_out[row * CST_NGRAM_SLOTS_PER_ROW + at] = tf[k];
+        }
+        base += __popc(lm);
+    }
+    if (lane == 0) {
+        n_out[row] = base;
+        len_out[row] = L;
+    }
+}
+
+extern "C" int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows, int32_t width,
+                                int64_t stride, int32_t use_eos, uint64_t* keys_out, int32_t* counts_out,
+                                int32_t* n_out, int32_t* len_out, int device, void* stream) {
+    if (n_rows < 0 || (n_rows > 0 && (!rows || !keys_out || !counts_out || !n_out || !len_out)))
+        return fail(CST_E_ARG, "cst_ngram_counts: NULL argument");
+    if (width < 1 || width > CST_MAX_ROW_WIDTH)
+        return fail(CST_E_RANGE, "cst_ngram_counts: row width %d outside [1, %d]", width, CST_MAX_ROW_WIDTH);
+    if (stride < width) return fail(CST_E_ARG, "cst_ngram_counts: stride < width");
+    if (dtype != CST_DTYPE_I32 && dtype != CST_DTYPE_I64) return fail(CST_E_ARG, "cst_ngram_counts: bad dtype");
+    if (n_rows == 0) return CST_OK;
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_ngram_counts: cannot select device %d", device);
+    const unsigned blocks = (unsigned)((n_rows + 7) / 8);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == CST_DTYPE_I32)
+        k_ngram_counts<int32_t><<<blocks, 256, 0, st>>>((const int32_t*)rows, n_rows, width, stride, use_eos,
+                                                       (u64*)keys_out, counts_out, n_out, len_out);
+    else
+        k_ngram_counts<int64_t><<<blocks, 256, 0, st>>>((const int64_t*)rows, n_rows, width, stride, use_eos,
+                                                       (u64*)keys_out, counts_out, n_out, len_out);
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+// ---------------------------------------------------------------------------
+// baseline (phase B): utils.py:292-322 and 219-224 on one group of S scores
+// ---------------------------------------------------------------------------
+// Sum of the k lowest of x[0..S) (ties broken by index, like a stable sort);
+// `sorted` is S doubles of scratch.  One warp.
+__device__ __forceinline__ double k_lowest_sum(const double* x, int S, int k, int lane, double* sorted) {
+    for (int i = lane; i < S; i += 32) {
+        const double xi = x[i];
+        int rank = 0;
+        for (int j = 0; j < S; ++j) {
+            const double xj = x[j];
+            rank += (xj < xi || (xj == xi && j < i)) ? 1 : 0;
+        }
+        sorted[rank] = xi;
+    }
+    __syncwarp();
+    double s = 0.0;
+    if (lane == 0) {
+        s = sorted[0];
+        for (int i = 1; i < k; ++i) s += sorted[i];   // ascending, the order np.mean(sorted[:k]) sees
+    }
+    __syncwarp();
+    return __shfl_sync(CST_FULL, s, 0);
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(CST_FULL, v, o);
+    return v;
+}
+
+// One warp turns the S scores of a group into rewards and the group's partial
+// statistics.  sc: S sampled scores (shared or global); other: greedy scores
+// (GREEDY) or bcmrscores row (SCB_GT); reward: global float out.
+__device__ __forceinline__ void baseline_group(const double* sc, const double* other, int S, int mode, int k,
+                                               int lane, double* sorted, float* reward, double& sum_m,
+                                               double& sum_b) {
+    double base = 0.0;
+    double sb = 0.0;
+    if (mode == CST_BASE_SCB_GT) {
+        base = k_lowest_sum(other, S, k, lane, sorted) / (double)k;
+        double a = 0.0;
+        for (int i = lane; i < S; i += 32) a += other[i];
+        sb = warp_sum(a);
+    } else if (mode == CST_BASE_SCB_SAMPLE) {
+        const double low = k_lowest_sum(sc, S, k, lane, sorted);
+        base = low / (double)k;
+        sb = low;
+    }
+    double am = 0.0, ag = 0.0;
+    for (int i = lane; i < S; i += 32) {
+        const double s = sc[i];
+        double r = s - base;
+        if (mode == CST_BASE_GREEDY) {
+            const double g = other[i];
+            r = s - g;
+            ag += g;
+        }
+        reward[i] = (float)r;
+        am += s;
+    }
+    sum_m = warp_sum(am);
+    if (mode == CST_BASE_GREEDY) sb = warp_sum(ag);
+    sum_b = sb;
+}
+
+// Deterministic fold of per-group partials by the last CTA to finish.
+// ctl[0] = CTA arrival counter, ctl[1] = bad-row counter; both return to 0.
+__device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* partials, int64_t n_groups,
+                                                   double n_m, double n_b, double* stats, double* red /*[2*nwarps]*/) {
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const u32 done = atomicAdd(&ctl[0], 1u);
+        s_last = (done == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double am = 0.0, ab = 0.0;
+    for (int64_t g = threadIdx.x; g < n_groups; g += blockDim.x) {
+        am += __ldcg(partials + 2 * g);
+        ab += __ldcg(partials + 2 * g + 1);
+    }
+    am = warp_sum(am);
+    ab = warp_sum(ab);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    if (lane == 0) { red[2 * warp] = am; red[2 * warp + 1] = ab; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tm = 0.0, tb = 0.0;
+        for (int w = 0; w < nw; ++w) { tm += red[2 * w]; tb += red[2 * w + 1]; }
+        stats[0] = tm;
+        stats[1] = tb;
+        stats[2] = n_m;
+        stats[3] = n_b;
+        stats[4] = (double)atomicExch(&ctl[1], 0u);
+        __threadfence();
+        ctl[0] = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// fused scoring kernel
+// ---------------------------------------------------------------------------
+struct ScoreParams {
+    const DfSlot* df;
+    u32 df_cap;
+    double idf_unseen;
+    const double* gauss;
+    const void* cand;
+    const void* greedy;
+    int64_t n_cand;
+    int cand_width;
+    int64_t cand_stride;
+    const void* refs;
+    int ref_width;
+    int64_t ref_stride;
+    const int64_t* ref_offsets;
+    int refs_per_video;   // exact count (ref_offsets == NULL) or declared maximum
+    int chunk_refs;       // refs staged per pass, <= 32
+    int64_t n_videos;
+    int cands_per_video;
+    int use_eos;
+    int mode;             // CST_BASE_* or -1: scores only
+    int scb_k;
+    const double* bcmr;
+    float* reward;
+    double* scores;
+    double* stats;
+    u32* ctl;
+    double* partials;
+    double n_m, n_b;
+    u32 tab_slots;        // power of two
+    int tab_shift;        // 32 - log2(tab_slots)
+};
+
+#define CST_MAX_WARPS 20
+
+// Phase R for one reference row (one warp).
+template <typename RT>
+__device__ __forceinline__ bool ref_phase(const ScoreParams& p, const RT* row, int rl, int lane, VidSlot* tab,
+                                          double* invn, int* lenr, u32* tokbuf) {
+    u64 key[4];
+    int L;
+    const bool bad = canon_row<RT>(row, p.ref_width, p.use_eos, lane, tokbuf, key, L);
+    int tf[4];
+    bool lead[4];
+    row_tf(key, lane, tf, lead);
+    u32 h[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
+    double idf[4];
+    df_probe4(p.df, p.df_cap, p.idf_unseen, key, h, lead, idf);
+
+    const u32 mask = p.tab_slots - 1u;
+    const u32 bit = 1u << rl;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (lead[k]) {
+            const u32 idx = vid_insert(tab, mask, h[k] >> p.tab_shift, key[k]);
+            atomicOr(&tab[idx].P, bit);
+            if (tf[k] > 1) {
+                atomicOr(&tab[idx].M, bit);
+                const u64 ck = count_key(idx, (u32)rl);
+                const u32 j = vid_insert(tab, mask, cst_hash(ck) >> p.tab_shift, ck);
+                tab[j].P = (u32)tf[k];
+            }
+        }
+    }
+    double n2[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
+        n2[k] = w * w;                                             // norm += vec ** 2
+    }
+    const double tot = warp_sum4_transposed(n2, lane);
+    if ((lane & 7) == 0) invn[lane_order(lane) * 32 + rl] = inv_norm_of(tot);
+    if (lane == 0) lenr[rl] = (L > 1) ? (L - 1) : 0;               // "length" = bigram count
+    return bad;
+}
+
+// Phase C for one candidate row (one warp): sum over the chunk's refs of
+// sum_n sim_n / (norm_h[n] norm_r[n]) * penalty  (not yet / n, / R, * 10).
+template <typename CT>
+__device__ __forceinline__ double cand_phase(const ScoreParams& p, const CT* row, int nref, int lane,
+                                             const VidSlot* tab, const double* invn, const int* lenr,
+                                             double* gh, u32* tokbuf, bool& bad) {
+    u64 key[4];
+    int L;
+    bad = canon_row<CT>(row, p.cand_width, p.use_eos, lane, tokbuf, key, L);
+    int tf[4];
+    bool lead[4];
+    row_tf(key, lane, tf, lead);
+    u32 h[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
+    double idf[4];
+    df_probe4(p.df, p.df_cap, p.idf_unseen, key, h, lead, idf);
+
+    // Gaussian length penalty against every ref of the chunk
+    const int lenh = (L > 1) ? (L - 1) : 0;
+    if (lane < nref) gh[lane] = __ldg(p.gauss + (lenh - lenr[lane] + CST_GAUSS_HALF));
+    __syncwarp();
+
+    double n2[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;
+        n2[k] = w * w;
+    }
+    const double invh = inv_norm_of(warp_sum4_transposed(n2, lane));
+
+    const u32 mask = p.tab_slots - 1u;
+    double num[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        double inner = 0.0;
+        if (lead[k]) {
+            const int idx = vid_find(tab, mask, h[k] >> p.tab_shift, key[k]);
+            if (idx >= 0) {
+                u32 P = tab[idx].P;
+                const u32 M = tab[idx].M;
+                const double* inv_k = invn + k * 32;
+                while (P) {
+                    const int r = __ffs(P) - 1;
+                    P &= P - 1u;
+                    const double cf = inv_k[r] * gh[r];
+                    if (!((M >> r) & 1u)) {
+                        inner += cf;                     // ref count 1: min(tf_h, 1) * 1
+                    } else {
+                        const u64 ck = count_key((u32)idx, (u32)r);
+                        const int j = vid_find(tab, mask, cst_hash(ck) >> p.tab_shift, ck);
+                        const int c = (int)tab[j].P;
+                        const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
+                        inner += (double)m * cf;
+                    }
+                }
+            }
+        }
+        num[k] = idf[k] * idf[k] * inner;
+    }
+    double t = warp_sum4_transposed(num, lane) * invh;
+    t += __shfl_xor_sync(CST_FULL, t, 16);
+    t += __shfl_xor_sync(CST_FULL, t, 8);
+    __syncwarp();
+    return t;
+}
+
+template <typename CT, typename RT>
+__global__ void __launch_bounds__(CST_MAX_WARPS * 32) k_score(const ScoreParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
+
+    VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
+    double* invn = reinterpret_cast<double*>(tab + p.tab_slots);   // [4][32]
+    double* gh_all = invn + 128;                                    // [nwarps][32]
+    double* sc = gh_all + nwarps * 32;                              // [n_local]
+    double* sorted = sc + n_local;                                  // [cands_per_video]
+    double* red = sorted + p.cands_per_video;                       // [2 * nwarps]
+    int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
+    u32* tok_all = reinterpret_cast<u32*>(lenr + 32);               // [nwarps][32]
+    double* gh = gh_all + warp * 32;
+    u32* tokbuf = tok_all + warp * 32;
+
+    for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
+        int64_t r0, r1;
+        if (p.ref_offsets) {
+            r0 = p.ref_offsets[video];
+            r1 = p.ref_offsets[video + 1];
+        } else {
+            r0 = video * p.refs_per_video;
+            r1 = r0 + p.refs_per_video;
+        }
+        const int R = (int)(r1 - r0);
+        for (int c = threadIdx.x; c < n_local; c += blockDim.x) sc[c] = 0.0;
+        u32 bad_rows = 0;
+
+        for (int64_t c0 = r0; c0 < r1; c0 += p.chunk_refs) {
+            const int nref = (int)((r1 - c0) < (int64_t)p.chunk_refs ? (r1 - c0) : (int64_t)p.chunk_refs);
+            {   // clear the video table
+                uint4* z = reinterpret_cast<uint4*>(tab);
+                for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+            }
+            __syncthreads();
+            for (int rl = warp; rl < nref; rl += nwarps) {
+                const RT* row = reinterpret_cast<const RT*>(p.refs) + (c0 + rl) * p.ref_stride;
+                if (ref_phase<RT>(p, row, rl, lane, tab, invn, lenr, tokbuf)) bad_rows += (lane == 0);
+            }
+            __syncthreads();
+            for (int c = warp; c < n_local; c += nwarps) {
+                const bool is_greedy = c >= p.cands_per_video;
+                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
+                const CT* base = reinterpret_cast<const CT*>(is_greedy ? p.greedy : p.cand);
+                bool bad;
+                const double t = cand_phase<CT>(p, base + ci * p.cand_stride, nref, lane, tab, invn, lenr, gh,
+                                                tokbuf, bad);
+                if (lane == 0) {
+                    sc[c] += t;
+                    if (bad && c0 == r0) ++bad_rows;
+                }
+            }
+            __syncthreads();
+        }
+
+        // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
+        for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
+            double s = sc[c] * 0.25;
+            s = (R > 0) ? s / (double)R : 0.0;
+            s *= 10.0;
+            sc[c] = s;
+            if (p.scores) {
+                const bool is_greedy = c >= p.cands_per_video;
+                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
+                p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
+            }
+        }
+        if (bad_rows && p.ctl) atomicAdd(&p.ctl[1], bad_rows);
+        __syncthreads();
+
+        if (p.mode >= 0 && warp == 0) {
+            const int S = p.cands_per_video;
+            const double* other = (p.mode == CST_BASE_GREEDY) ? (sc + S)
+                                  : (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : nullptr;
+            double sm, sb;
+            baseline_group(sc, other, S, p.mode, p.scb_k, lane, sorted, p.reward + video * S, sm, sb);
+            if (lane == 0) {
+                p.partials[2 * video] = sm;
+                p.partials[2 * video + 1] = sb;
+            }
+        }
+        __syncthreads();
+    }
+    if (p.mode >= 0) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
+}
+
+// Standalone baseline over (n_groups, S) scores: one warp per group.
+__global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, const double* __restrict__ other,
+                                             int64_t n_groups, int S, int mode, int k, float* reward,
+                                             double* stats, u32* ctl, double* partials, double n_m, double n_b) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    double* red = reinterpret_cast<double*>(smem);   // [8]
+    double* sorted_all = red + 8;                    // [4][S]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t g = (int64_t)blockIdx.x * 4 + warp; g < n_groups; g += (int64_t)gridDim.x * 4) {
+        double sm, sb;
+        baseline_group(scores + g * S, other ? other + g * S : nullptr, S, mode, k, lane, sorted_all + warp * S,
+                       reward + g * S, sm, sb);
+        if (lane == 0) {
+            partials[2 * g] = sm;
+            partials[2 * g + 1] = sb;
+        }
+    }
+    fold_stats_if_last(ctl, partials, n_groups, n_m, n_b, stats, red);
+}
+
+// ---------------------------------------------------------------------------
+// host side of scoring
+// ---------------------------------------------------------------------------
+static int grams_per_row(int width) {
+    int w = width < 32 ? width : 32, g = 0;
+    for (int k = 1; k <= 4; ++k) g += (w - k + 1 > 0) ? (w - k + 1) : 0;
+    return g;
+}
+
+static u32 next_pow2(u32 x) {
+    u32 p = 1;
+    while (p < x) p <<= 1;
+    return p;
+}
+
+extern "C" int64_t cst_reward_scratch_bytes(int64_t n_groups) {
+    if (n_groups < 0) return -1;
+    return 256 + 16 * n_groups;
+}
+
+static void stat_counts(int mode, int64_t n_cand, int seq_per_img, int k, double& n_m, double& n_b) {
+    n_m = (double)n_cand;
+    switch (mode) {
+        case CST_BASE_GREEDY: n_b = (double)n_cand; break;
+        case CST_BASE_SCB_GT: n_b = (double)n_cand; break;
+        case CST_BASE_SCB_SAMPLE: n_b = (double)(n_cand / seq_per_img) * (double)k; break;
+        default: n_b = 1.0; break;   // b_score = 0 / 1
+    }
+}
+
+template <typename CT, typename RT>
+static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st) {
+    static thread_local size_t configured[64] = {0};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= 64 || configured[dev] < smem) {
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CT, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (dev < 64) configured[dev] = smem;
+    }
+    const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+    k_score<CT, RT><<<grid, threads, smem, st>>>(p);
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+static int score_common(const char* who, const cst_df_table* t, const void* cand, const void* greedy,
+                        int32_t cand_dtype, int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                        const void* refs, int32_t ref_dtype, int32_t ref_width, int64_t ref_stride,
+                        const int64_t* ref_offsets, int32_t refs_per_video, int64_t n_videos,
+                        int32_t cands_per_video, int32_t use_eos, int mode, int scb_k, const double* bcmr,
+                        float* reward, double* scores, double* stats, void* scratch, int64_t scratch_bytes,
+                        cudaStream_t st) {
+    if (!t) return fail(CST_E_ARG, "%s: table is NULL", who);
+    if (n_cand < 0 || n_videos < 0 || cands_per_video < 1) return fail(CST_E_ARG, "%s: negative size", who);
+    if (n_cand != n_videos * (int64_t)cands_per_video)
+        return fail(CST_E_ARG, "%s: n_cand (%lld) != n_videos (%lld) * cands_per_video (%d)", who,
+                    (long long)n_cand, (long long)n_videos, cands_per_video);
+    if (cand_width < 1 || cand_width > CST_MAX_ROW_WIDTH || ref_width < 1 || ref_width > CST_MAX_ROW_WIDTH)
+        return fail(CST_E_RANGE, "%s: row widths %d/%d outside [1, %d]", who, cand_width, ref_width,
+                    CST_MAX_ROW_WIDTH);
+    if (cand_stride < cand_width || ref_stride < ref_width) return fail(CST_E_ARG, "%s: stride < width", who);
+    if ((cand_dtype != CST_DTYPE_I32 && cand_dtype != CST_DTYPE_I64) ||
+        (ref_dtype != CST_DTYPE_I32 && ref_dtype != CST_DTYPE_I64))
+        return fail(CST_E_ARG, "%s: bad dtype", who);
+    if (refs_per_video < 0 || (refs_per_video == 0 && !ref_offsets))
+        return fail(CST_E_ARG, "%s: refs_per_video must be > 0", who);
+    if (cands_per_video > 4096) return fail(CST_E_RANGE, "%s: cands_per_video %d > 4096", who, cands_per_video);
+    if (n_cand == 0) {
+        return CST_OK;
+    }
+    if (!cand || !refs) return fail(CST_E_ARG, "%s: NULL rows", who);
+    if (mode == CST_BASE_GREEDY && !greedy) return fail(CST_E_ARG, "%s: greedy rows required", who);
+
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "%s: cannot select device %d", who, t->device);
+
+    ScoreParams p;
+    memset(&p, 0, sizeof(p));
+    p.df = t->slots;
+    p.df_cap = t->capacity;
+    p.idf_unseen = t->idf_unseen;
+    p.gauss = t->gauss;
+    p.cand = cand;
+    p.greedy = greedy;
+    p.n_cand = n_cand;
+    p.cand_width = cand_width;
+    p.cand_stride = cand_stride;
+    p.refs = refs;
+    p.ref_width = ref_width;
+    p.ref_stride = ref_stride;
+    p.ref_offsets = ref_offsets;
+    p.refs_per_video = refs_per_video;
+    p.chunk_refs = refs_per_video < 32 ? (refs_per_video < 1 ? 1 : refs_per_video) : 32;
+    p.n_videos = n_videos;
+    p.cands_per_video = cands_per_video;
+    p.use_eos = use_eos ? 1 : 0;
+    p.mode = mode;
+    p.scb_k = scb_k;
+    p.bcmr = bcmr;
+    p.reward = reward;
+    p.scores = scores;
+    p.stats = stats;
+    if (mode >= 0 || scratch) {
+        const int64_t need = (mode >= 0) ? cst_reward_scratch_bytes(n_videos) : 256;
+        if (!scratch || scratch_bytes < need)
+            return fail(CST_E_ARG, "%s: scratch too small (%lld < %lld bytes)", who, (long long)scratch_bytes,
+                        (long long)need);
+        p.ctl = reinterpret_cast<u32*>(scratch);   // [1] also collects bad rows in scores-only mode
+        p.partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
+        if (mode >= 0) stat_counts(mode, n_cand, cands_per_video, scb_k, p.n_m, p.n_b);
+    }
+    // every n-gram instance of the staged refs gets at most one slot (plus, for an
+    // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
+    const u32 worst = (u32)p.chunk_refs * (u32)grams_per_row(ref_width);
+    p.tab_slots = next_pow2(worst + worst / 4 + 8);
+    if (p.tab_slots < 64) p.tab_slots = 64;
+    p.tab_shift = 32 - __builtin_ctz(p.tab_slots);
+
+    const int n_local = cands_per_video * (greedy ? 2 : 1);
+    int nwarps = p.chunk_refs > n_local ? p.chunk_refs : n_local;
+    if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
+    if (nwarps < 4) nwarps = 4;
+    const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
+                        (size_t)nwarps * 32 * sizeof(double) + (size_t)n_local * sizeof(double) +
+                        (size_t)cands_per_video * sizeof(double) + (size_t)2 * nwarps * sizeof(double) +
+                        32 * sizeof(int) + (size_t)nwarps * 32 * sizeof(u32);
+    if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
+
+    const int threads = nwarps * 32;
+    if (cand_dtype == CST_DTYPE_I32 && ref_dtype == CST_DTYPE_I32) return launch_score<int32_t, int32_t>(p, threads, smem, st);
+    if (cand_dtype == CST_DTYPE_I64 && ref_dtype == CST_DTYPE_I64) return launch_score<int64_t, int64_t>(p, threads, smem, st);
+    if (cand_dtype == CST_DTYPE_I64 && ref_dtype == CST_DTYPE_I32) return launch_score<int64_t, int32_t>(p, threads, smem, st);
+    return launch_score<int32_t, int64_t>(p, threads, smem, st);
+}
+
+extern "C" int cst_cider_scores(const cst_df_table* table, const void* cand, const void* greedy,
+                                int32_t cand_dtype, int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                                const void* refs, int32_t ref_dtype, int32_t ref_width, int64_t ref_stride,
+                                const int64_t* ref_offsets, int32_t refs_per_video, int64_t n_videos,
+                                int32_t cands_per_video, int32_t use_eos, double* scores_out, void* stream) {
+    if (n_cand > 0 && !scores_out) return fail(CST_E_ARG, "cst_cider_scores: scores_out is NULL");
+    return score_common("cst_cider_scores", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs,
+                        ref_dtype, ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video,
+                        use_eos, -1, 0, nullptr, nullptr, scores_out, nullptr, nullptr, 0, (cudaStream_t)stream);
+}
+
+static int check_baseline_args(const char* who, int mode, int seq_per_img, int scb_k, const void* other) {
+    if (mode < CST_BASE_NONE || mode > CST_BASE_SCB_SAMPLE) return fail(CST_E_ARG, "%s: unknown baseline mode %d", who, mode);
+    if (seq_per_img < 1) return fail(CST_E_ARG, "%s: seq_per_img < 1", who);
+    if ((mode == CST_BASE_SCB_GT || mode == CST_BASE_SCB_SAMPLE) && (scb_k < 1 || scb_k > seq_per_img))
+        return fail(CST_E_ARG, "%s: scb_k %d outside [1, %d]", who, scb_k, seq_per_img);
+    if (mode == CST_BASE_SCB_GT && !other) return fail(CST_E_ARG, "%s: bcmrscores required", who);
+    return CST_OK;
+}
+
+extern "C" int cst_scb_apply(const double* scores, const double* other, int64_t n_rows, int32_t seq_per_img,
+                             int32_t mode, int32_t scb_k, float* reward_out, double* stats_out, void* scratch,
+                             int64_t scratch_bytes, int device, void* stream) {
+    int rc = check_baseline_args("cst_scb_apply", mode, seq_per_img, scb_k, other);
+    if (rc != CST_OK) return rc;
+    if (n_rows < 0) return fail(CST_E_ARG, "cst_scb_apply: n_rows < 0");
+    if (n_rows == 0) return CST_OK;
+    if (!scores || !reward_out || !stats_out) return fail(CST_E_ARG, "cst_scb_apply: NULL argument");
+    if (mode == CST_BASE_GREEDY && !other) return fail(CST_E_ARG, "cst_scb_apply: greedy scores required");
+    if (seq_per_img > 4096) return fail(CST_E_RANGE, "cst_scb_apply: seq_per_img %d > 4096", seq_per_img);
+    if (!scratch || scratch_bytes < cst_reward_scratch_bytes(n_rows))
+        return fail(CST_E_ARG, "cst_scb_apply: scratch too small");
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_scb_apply: cannot select device %d", device);
+    double n_m, n_b;
+    stat_counts(mode, n_rows * seq_per_img, seq_per_img, scb_k, n_m, n_b);
+    const size_t smem = (8 + (size_t)4 * seq_per_img) * sizeof(double);
+    if (smem > 48 * 1024) {
+        CUDA_TRY(cudaFuncSetAttribute(k_scb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    int64_t blocks = (n_rows + 3) / 4;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    k_scb<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
+        scores, other, n_rows, seq_per_img, mode, scb_k, reward_out, stats_out, reinterpret_cast<u32*>(scratch),
+        reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256), n_m, n_b);
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+extern "C" int cst_reward(const cst_df_table* table, const void* cand, const void* greedy, int32_t cand_dtype,
+                          int64_t n_cand, int32_t cand_width, int64_t cand_stride, const void* refs,
+                          int32_t ref_dtype, int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
+                          int32_t refs_per_video, int64_t n_videos, int32_t cands_per_video, int32_t use_eos,
+                          int32_t mode, int32_t seq_per_img, int32_t scb_k, const double* bcmrscores,
+                          float* reward_out, double* scores_out, double* stats_out, void* scratch,
+                          int64_t scratch_bytes, void* stream) {
+    int rc = check_baseline_args("cst_reward", mode, seq_per_img, scb_k, bcmrscores);
+    if (rc != CST_OK) return rc;
+    if (n_cand > 0 && (!reward_out || !stats_out)) return fail(CST_E_ARG, "cst_reward: NULL output");
+    if (n_cand % seq_per_img != 0)
+        return fail(CST_E_ARG, "cst_reward: n_cand %lld is not a multiple of seq_per_img %d", (long long)n_cand,
+                    seq_per_img);
+    if (cands_per_video == seq_per_img) {
+        return score_common("cst_reward", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs,
+                            ref_dtype, ref_width, ref_stride, ref_offsets, refs_per_video, n_videos,
+                            cands_per_video, use_eos, mode, scb_k, bcmrscores, reward_out, scores_out, stats_out,
+                            scratch, scratch_bytes, (cudaStream_t)stream);
+    }
+    // baseline rows do not coincide with videos (expand_feat == 0): score, then baseline
+    if (!scores_out) return fail(CST_E_ARG, "cst_reward: scores_out is required when cands_per_video != seq_per_img");
+    rc = score_common("cst_reward", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
+                      ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, -1, 0,
+                      nullptr, nullptr, scores_out, nullptr, scratch, scratch_bytes, (cudaStream_t)stream);
+    if (rc != CST_OK) return rc;
+    const double* other = (mode == CST_BASE_GREEDY) ? scores_out + n_cand : bcmrscores;
+    return cst_scb_apply(scores_out, other, n_cand / seq_per_img, seq_per_img, mode, scb_k, reward_out, stats_out,
+                         scratch, scratch_bytes, table->device, stream);
+}
+
+// ---------------------------------------------------------------------------
+// device-side document frequency (compute_ciderdf.py:56-70 on packed keys)
+// ---------------------------------------------------------------------------
+// Insert into a shared-memory key set; true iff this call created the entry.
+__device__ __forceinline__ bool set_insert_new(u64* keys, u32 mask, u32 idx, u64 key) {
+    for (;;) {
+        u64 cur = *reinterpret_cast<volatile u64*>(&keys[idx]);
+        if (cur == key) return false;
+        if (cur == 0ull) {
+            u64 old = atomicCAS(&keys[idx], 0ull, key);
+            if (old == 0ull) return true;
+            if (old == key) return false;
+        }
+        idx = (idx + 1) & mask;
+    }
+}
+
+// One CTA per video: the set union of its refs' n-grams is formed in shared memory
+// (compute_ciderdf.py:66-67); each member then adds 1 to its global counter (:68).
+template <typename T>
+__global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, int width, int64_t stride,
+                                                  int use_eos, const int64_t* __restrict__ video_offsets,
+                                                  int64_t n_videos, u32 set_slots, int set_shift, u64* g_keys,
+                                                  u32* g_cnt, u32 g_cap, u32* n_unique, u32* n_bad) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* set = reinterpret_cast<u64*>(smem);
+    u32* tok_all = reinterpret_cast<u32*>(set + set_slots);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    u32* tokbuf = tok_all + warp * 32;
+    for (int64_t video = blockIdx.x; video < n_videos; video += gridDim.x) {
+        for (u32 i = threadIdx.x; i < set_slots; i += blockDim.x) set[i] = 0ull;
+        __syncthreads();
+        const int64_t r0 = video_offsets[video], r1 = video_offsets[video + 1];
+        for (int64_t r = r0 + warp; r < r1; r += nwarps) {
+            u64 key[4];
+            int L;
+            const bool bad = canon_row<T>(rows + r * stride, width, use_eos, lane, tokbuf, key, L);
+            if (bad && lane == 0) atomicAdd(n_bad, 1u);
+            int tf[4];
+            bool lead[4];
+            row_tf(key, lane, tf, lead);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                if (!lead[k]) continue;
+                const u32 h = cst_hash(key[k]);
+                if (!set_insert_new(set, set_slots - 1u, h >> set_shift, key[k])) continue;
+                u32 s = cst_slot(h, g_cap);
+                for (;;) {
+                    u64 cur = *reinterpret_cast<volatile u64*>(&g_keys[s]);
+                    if (cur == key[k]) break;
+                    if (cur == 0ull) {
+                        u64 old = atomicCAS(&g_keys[s], 0ull, key[k]);
+                        if (old == 0ull) { atomicAdd(n_unique, 1u); break; }
+                        if (old == key[k]) break;
+                    }
+                    s = (s + 1 == g_cap) ? 0u : s + 1;
+                }
+                atomicAdd(&g_cnt[s], 1u);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// Move the counted keys into the final table (own capacity), idf looked up from
+// the caller's float64 LUT so it is bit-identical to the scorer's numpy value.
+__global__ void k_df_rehash(const u64* __restrict__ g_keys, const u32* __restrict__ g_cnt, u32 g_cap,
+                            const double* __restrict__ idf_by_df, DfSlot* slots, double* df, u32 cap) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g_cap) return;
+    const u64 key = g_keys[i];
+    if (key == 0ull) return;
+    const u32 c = g_cnt[i];
+    u32 s = cst_slot(cst_hash(key), cap);
+    for (;;) {
+        u64 old = atomicCAS(reinterpret_cast<u64*>(&slots[s].key), 0ull, key);
+        if (old == 0ull) break;
+        s = (s + 1 == cap) ? 0u : s + 1;
+    }
+    slots[s].idf = idf_by_df[c];
+    df[s] = (double)c;
+}
+
+extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n_rows, int32_t width,
+                                      int64_t stride, const int64_t* video_offsets, int64_t n_videos,
+                                      int32_t use_eos, const double* idf_by_df, int device, cst_df_table** out) {
+    if (!out) return fail(CST_E_ARG, "cst_df_build_from_rows: out is NULL");
+    *out = nullptr;
+    if (n_rows < 0 || n_videos < 1 || !video_offsets || !idf_by_df || (n_rows > 0 && !rows))
+        return fail(CST_E_ARG, "cst_df_build_from_rows: bad argument");
+    if (width < 1 || width > CST_MAX_ROW_WIDTH)
+        return fail(CST_E_RANGE, "cst_df_build_from_rows: row width %d outside [1, %d]", width, CST_MAX_ROW_WIDTH);
+    if (stride < width) return fail(CST_E_ARG, "cst_df_build_from_rows: stride < width");
+    if (dtype != CST_DTYPE_I32 && dtype != CST_DTYPE_I64) return fail(CST_E_ARG, "cst_df_build_from_rows: bad dtype");
+    if (n_videos > 0x7fffffffLL) return fail(CST_E_RANGE, "cst_df_build_from_rows: too many videos");
+    int64_t max_refs = 0;
+    if (video_offsets[0] != 0 || video_offsets[n_videos] != n_rows)
+        return fail(CST_E_ARG, "cst_df_build_from_rows: video_offsets must span [0, n_rows]");
+    for (int64_t v = 0; v < n_videos; ++v) {
+        const int64_t c = video_offsets[v + 1] - video_offsets[v];
+        if (c < 0) return fail(CST_E_ARG, "cst_df_build_from_rows: video_offsets not monotone at %lld", (long long)v);
+        if (c > max_refs) max_refs = c;
+    }
+    const int g_row = grams_per_row(width);
+    const int64_t per_video = max_refs * g_row;
+    if (per_video + per_video / 4 + 8 > (1 << 14))
+        return fail(CST_E_RANGE, "cst_df_build_from_rows: %lld refs in one video exceed the shared-memory set",
+                    (long long)max_refs);
+    const int64_t instances = n_rows * (int64_t)g_row;
+    if (2 * instances + 16 > 0xffffffffLL) return fail(CST_E_RANGE, "cst_df_build_from_rows: corpus too large");
+
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_df_build_from_rows: cannot select device %d", device);
+
+    const u32 want = (u32)(per_video + per_video / 4 + 8);
+    const u32 set_slots = next_pow2(want < 64 ? 64 : want);
+    const int set_shift = 32 - __builtin_ctz(set_slots);
+    const u32 g_cap = (u32)(2 * instances + 16);
+    u64* g_keys = nullptr;
+    u32* g_cnt = nullptr;
+    u32* counters = nullptr;      // [0] unique keys, [1] bad rows
+    int64_t* d_off = nullptr;
+    double* d_lut = nullptr;
+    cst_df_table* t = nullptr;
+    int rc = CST_OK;
+    cudaError_t e = cudaSuccess;
+    u32 h_counters[2] = {0, 0};
+    const size_t smem = (size_t)set_slots * sizeof(u64) + 8 * 32 * sizeof(u32);
+    const unsigned grid = (unsigned)(n_videos < 148 * 32 ? n_videos : 148 * 32);
+#define BUILD_TRY(expr)                                                                              \
+    do {                                                                                             \
+        e = (expr);                                                                                  \
+        if (e != cudaSuccess) {                                                                      \
+            rc = fail(e == cudaErrorMemoryAllocation ? CST_E_NOMEM : CST_E_CUDA, "%s failed: %s", #expr, \
+                      cudaGetErrorString(e));                                                        \
+            goto done;                                                                               \
+        }                                                                                            \
+    } while (0)
+    BUILD_TRY(cudaMalloc(&g_keys, (size_t)g_cap * sizeof(u64)));
+    BUILD_TRY(cudaMalloc(&g_cnt, (size_t)g_cap * sizeof(u32)));
+    BUILD_TRY(cudaMalloc(&counters, 2 * sizeof(u32)));
+    BUILD_TRY(cudaMalloc(&d_off, (size_t)(n_videos + 1) * sizeof(int64_t)));
+    BUILD_TRY(cudaMalloc(&d_lut, (size_t)(n_videos + 1) * sizeof(double)));
+    BUILD_TRY(cudaMemset(g_keys, 0, (size_t)g_cap * sizeof(u64)));
+    BUILD_TRY(cudaMemset(g_cnt, 0, (size_t)g_cap * sizeof(u32)));
+    BUILD_TRY(cudaMemset(counters, 0, 2 * sizeof(u32)));
+    BUILD_TRY(cudaMemcpy(d_off, video_offsets, (size_t)(n_videos + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
+    BUILD_TRY(cudaMemcpy(d_lut, idf_by_df, (size_t)(n_videos + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    if (dtype == CST_DTYPE_I32) {
+        BUILD_TRY(cudaFuncSetAttribute(k_df_build<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_df_build<int32_t><<<grid, 256, smem>>>((const int32_t*)rows, width, stride, use_eos ? 1 : 0, d_off,
+                                                 n_videos, set_slots, set_shift, g_keys, g_cnt, g_cap, counters,
+                                                 counters + 1);
+    } else {
+        BUILD_TRY(cudaFuncSetAttribute(k_df_build<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_df_build<int64_t><<<grid, 256, smem>>>((const int64_t*)rows, width, stride, use_eos ? 1 : 0, d_off,
+                                                 n_videos, set_slots, set_shift, g_keys, g_cnt, g_cap, counters,
+                                                 counters + 1);
+    }
+    BUILD_TRY(cudaGetLastError());
+    BUILD_TRY(cudaMemcpy(h_counters, counters, sizeof(h_counters), cudaMemcpyDeviceToHost));
+    if (h_counters[1] != 0) {
+        rc = fail(CST_E_RANGE, "cst_df_build_from_rows: %u rows hold token ids outside [0, %d]", h_counters[1],
+                  CST_MAX_TOKEN_ID);
+        goto done;
+    }
+    rc = table_alloc(device, df_capacity_for((int64_t)h_counters[0]), idf_by_df[0], &t);
+    if (rc != CST_OK) goto done;
+    BUILD_TRY(cudaMemset(t->slots, 0, (size_t)t->capacity * sizeof(DfSlot)));
+    BUILD_TRY(cudaMemset(t->df, 0, (size_t)t->capacity * sizeof(double)));
+    k_df_rehash<<<(g_cap + 255) / 256, 256>>>(g_keys, g_cnt, g_cap, d_lut, t->slots, t->df, t->capacity);
+    BUILD_TRY(cudaGetLastError());
+    BUILD_TRY(cudaDeviceSynchronize());
+    t->size = (int64_t)h_counters[0];
+done:
+#undef BUILD_TRY
+    cudaFree(g_keys);
+    cudaFree(g_cnt);
+    cudaFree(counters);
+    cudaFree(d_off);
+    cudaFree(d_lut);
+    if (rc != CST_OK) {
+        if (t) cst_df_destroy(t);
+        return rc;
+    }
+    *out = t;
+    return CST_OK;
+}

@@ -1,0 +1,236 @@
+"""Reward functions of the RL loop on the GPU, with the reference's signatures.
+
+Mirrors ``utils.get_cst_reward`` (``utils.py:229-324``) and
+``utils.get_self_critical_reward`` (``utils.py:169-226``): same argument names,
+meaning and error behaviour; the work happens in one launch of the sm_100a
+kernels behind the C ABI (``include/cst_reward.h``) and the results stay on the
+device:
+
+* ``rewards``  -> float32 CUDA tensor ``(N, T)``, an ``expand``-ed view of the
+  per-caption column (the reference's ``np.repeat(...)``, ``utils.py:224, 322``,
+  followed by ``torch.from_numpy(reward).float().cuda()``, ``train.py:209``);
+* ``m_score``, ``b_score``/``g_score`` -> 0-dim float64 CUDA tensors
+  (``float(x)`` at log time, ``train.py:229-233``).
+
+``model_res`` / ``greedy_res`` may be CUDA tensors (no host round trip, the
+``.cpu().numpy()`` of ``train.py:185,198-199`` is simply dropped) or numpy arrays
+(drop-in for the unmodified call sites; they are uploaded).  ``data_gts`` may be
+the reference's list of per-video ``(ncap, W)`` arrays (``dataloader.py:138-139``),
+a CUDA tensor ``(B, R, W)``, or a :class:`RefSet` kept on the device.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import lib, check
+from .ciderd import CiderD
+from .df_table import _row_dtype
+
+
+class RefSet:
+    """Reference rows resident on the device: ``rows`` (total, W) CUDA int tensor,
+    video v owning rows ``offsets[v]:offsets[v+1]`` (None = uniform ``per_video``)."""
+
+    def __init__(self, rows, offsets=None, per_video=None):
+        if not (torch.is_tensor(rows) and rows.is_cuda and rows.dim() == 2):
+            raise ValueError('RefSet rows must be a 2-D CUDA tensor')
+        if rows.stride(1) != 1:
+            rows = rows.contiguous()
+        self.rows = rows
+        if offsets is None:
+            if not per_video or rows.shape[0] % per_video:
+                raise ValueError('uniform RefSet needs per_video dividing the row count')
+            self.offsets = None
+            self.max_refs = int(per_video)
+            self.n_videos = rows.shape[0] // per_video
+        else:
+            off = np.ascontiguousarray(offsets.cpu().numpy() if torch.is_tensor(offsets) else offsets,
+                                       dtype=np.int64)
+            if off[0] != 0 or off[-1] != rows.shape[0] or np.any(np.diff(off) < 0):
+                raise ValueError('offsets must rise from 0 to the row count')
+            self.offsets = torch.from_numpy(off).to(rows.device)
+            self.max_refs = int(np.diff(off).max()) if len(off) > 1 else 0
+            self.n_videos = len(off) - 1
+
+    @classmethod
+    def from_list(cls, data_gts, device):
+        counts = [len(g) for g in data_gts]
+        rows = np.concatenate([np.asarray(g).reshape(len(g), -1) for g in data_gts], axis=0)
+        if rows.dtype.kind not in 'iu':
+            if np.any(rows != np.floor(rows)):
+                raise ValueError('reference rows must hold integer token ids')
+        rows = _narrow(np.ascontiguousarray(rows, dtype=np.int64))
+        t = torch.from_numpy(rows).to(device)
+        if len(set(counts)) == 1:
+            return cls(t, per_video=counts[0])
+        return cls(t, offsets=np.concatenate([[0], np.cumsum(counts)]))
+
+    @classmethod
+    def coerce(cls, data_gts, device):
+        if isinstance(data_gts, cls):
+            return data_gts
+        if torch.is_tensor(data_gts):
+            if data_gts.dim() != 3:
+                raise ValueError('a reference tensor must be (videos, refs, width)')
+            b, r, w = data_gts.shape
+            return cls(data_gts.to(device).reshape(b * r, w), per_video=r)
+        return cls.from_list(data_gts, device)
+
+
+def _narrow(rows):
+    """Host int64 rows -> int32 when every id fits (halves the upload; ids outside
+    [0, 65534] are rejected by the kernels either way)."""
+    if rows.size and (rows.max() > np.iinfo(np.int32).max or rows.min() < np.iinfo(np.int32).min):
+        return rows
+    return rows.astype(np.int32)
+
+
+def _rows_on_device(x, device):
+    if torch.is_tensor(x):
+        t = x.to(device)
+    else:
+        x = np.ascontiguousarray(x)
+        if x.dtype == np.int64:
+            x = _narrow(x)
+        t = torch.from_numpy(x).to(device)
+    if t.dtype not in (torch.int32, torch.int64):
+        t = t.to(torch.int64)
+    if t.dim() != 2:
+        raise ValueError('caption rows must be 2-D (captions, tokens)')
+    if t.stride(1) != 1:
+        t = t.contiguous()
+    return t
+
+
+_scratch = {}
+
+
+def _scratch_for(device, n_groups):
+    """Zero-initialised scratch the kernels leave clean (see cst_reward_scratch_bytes)."""
+    need = int(lib.cst_reward_scratch_bytes(n_groups))
+    buf = _scratch.get(device)
+    if buf is None or buf.numel() < need:
+        buf = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=device)
+        _scratch[device] = buf
+    return buf
+
+
+def _stream(device):
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _launch_reward(scorer, sampled, greedy, refs, cands_per_video, use_eos, mode, seq_per_img, k,
+                   bcmr, want_scores):
+    dev = scorer.table.device
+    n = sampled.shape[0]
+    n_videos = n // cands_per_video
+    if n_videos * cands_per_video != n or n_videos > refs.n_videos:
+        raise ValueError('caption count %d does not match %d videos x %d' % (n, refs.n_videos, cands_per_video))
+    reward = torch.empty(n, dtype=torch.float32, device=dev)
+    stats = torch.empty(_lib.N_STATS, dtype=torch.float64, device=dev)
+    fused = cands_per_video == seq_per_img
+    scores = None
+    if want_scores or not fused:
+        scores = torch.empty(n * (2 if greedy is not None else 1), dtype=torch.float64, device=dev)
+    scratch = _scratch_for(dev, max(n_videos, n // seq_per_img))
+    check(lib.cst_reward(
+        scorer.table.handle, sampled.data_ptr(), greedy.data_ptr() if greedy is not None else None,
+        _row_dtype(sampled), n, sampled.shape[1], sampled.stride(0),
+        refs.rows.data_ptr(), _row_dtype(refs.rows), refs.rows.shape[1], refs.rows.stride(0),
+        refs.offsets.data_ptr() if refs.offsets is not None else None, refs.max_refs, n_videos,
+        cands_per_video, int(use_eos), mode, seq_per_img, k,
+        bcmr.data_ptr() if bcmr is not None else None,
+        reward.data_ptr(), scores.data_ptr() if scores is not None else None, stats.data_ptr(),
+        scratch.data_ptr(), scratch.numel(), _stream(dev)))
+    return reward, stats, scores
+
+
+def _finish(reward, stats, width):
+    rewards = reward.unsqueeze(1).expand(reward.shape[0], width)
+    return rewards, stats[0] / stats[2], stats[1] / stats[3]
+
+
+def _need_scorer(bcmr_scorer):
+    if not isinstance(bcmr_scorer, CiderD):
+        raise TypeError('the GPU reward path implements the CiderD scorer only '
+                        '(utils.py:194,260 dispatch); got %r' % type(bcmr_scorer).__name__)
+    return bcmr_scorer
+
+
+def get_self_critical_reward(model_res, greedy_res, data_gts, bcmr_scorer, expand_feat=0,
+                             seq_per_img=20, use_eos=0, return_stats=False):
+    """``utils.py:169-226``: reward = CIDEr-D(sampled) - CIDEr-D(greedy)."""
+    scorer = _need_scorer(bcmr_scorer)
+    dev = scorer.table.device
+    sampled = _rows_on_device(model_res, dev)
+    greedy = _rows_on_device(greedy_res, dev)
+    if greedy.shape[0] != sampled.shape[0]:
+        raise ValueError('greedy_res and model_res differ in caption count')
+    if greedy.shape[1] != sampled.shape[1] or greedy.dtype != sampled.dtype or \
+            greedy.stride(0) != sampled.stride(0):
+        # the ABI takes one geometry for both row sets: pad the narrower one with <end>
+        w = max(greedy.shape[1], sampled.shape[1])
+        dt = torch.int64 if torch.int64 in (greedy.dtype, sampled.dtype) else torch.int32
+        sampled = torch.nn.functional.pad(sampled.to(dt), (0, w - sampled.shape[1])).contiguous()
+        greedy = torch.nn.functional.pad(greedy.to(dt), (0, w - greedy.shape[1])).contiguous()
+    refs = RefSet.coerce(data_gts, dev)
+    per_video = seq_per_img if expand_feat == 1 else 1
+    reward, stats, _ = _launch_reward(scorer, sampled, greedy, refs, per_video, use_eos,
+                                      _lib.BASE_GREEDY, per_video, 0, None, False)
+    out = _finish(reward, stats, model_res.shape[1])
+    return out + (stats,) if return_stats else out
+
+
+def get_cst_reward(model_res, data_gts, bcmr_scorer, bcmrscores=None, expand_feat=0, seq_per_img=20,
+                   scb_captions=20, scb_baseline=1, use_eos=0, use_mixer=0, return_stats=False):
+    """``utils.py:229-324``.  ``scb_baseline``: 1 = baseline from the GT consensus
+    scores ``bcmrscores``, 2 = from the model samples' own scores; the baseline is
+    the mean of the ``scb_captions`` lowest scores of the video's row."""
+    scorer = _need_scorer(bcmr_scorer)
+    dev = scorer.table.device
+    width = model_res.shape[1]
+
+    if scb_captions > 0:
+        if scb_baseline == 1:
+            mode = _lib.BASE_SCB_GT
+            if bcmrscores is None:
+                raise ValueError('bcmrscores is not set!')
+        elif scb_baseline == 2:
+            mode = _lib.BASE_SCB_SAMPLE
+        else:
+            raise ValueError('unknown scb_baseline!')
+        k = min(int(scb_captions), seq_per_img)      # numpy's [:k] clamps the same way
+    else:
+        mode, k = _lib.BASE_NONE, 0
+
+    bcmr = None
+    if bcmrscores is not None:
+        bcmr = bcmrscores if torch.is_tensor(bcmrscores) else torch.from_numpy(np.asarray(bcmrscores))
+        bcmr = bcmr.to(dev, torch.float64).contiguous()
+
+    if bcmrscores is None or use_mixer == 1:
+        sampled = _rows_on_device(model_res, dev)
+        if sampled.shape[0] % seq_per_img:
+            raise ValueError('cannot reshape %d scores into rows of %d' % (sampled.shape[0], seq_per_img))
+        refs = RefSet.coerce(data_gts, dev)
+        per_video = seq_per_img if expand_feat == 1 else 1
+        if bcmr is not None and mode == _lib.BASE_SCB_GT and bcmr.numel() != sampled.shape[0]:
+            raise ValueError('bcmrscores must hold one score per sampled caption')
+        reward, stats, _ = _launch_reward(scorer, sampled, None, refs, per_video, use_eos, mode,
+                                          seq_per_img, k, bcmr if mode == _lib.BASE_SCB_GT else None,
+                                          False)
+    else:
+        # WXE (utils.py:286-288): the precomputed consensus scores ARE the scores
+        if bcmr.dim() != 2 or bcmr.shape[1] != seq_per_img:
+            raise ValueError('bcmrscores must be (videos, seq_per_img)')
+        n_rows = bcmr.shape[0]
+        reward = torch.empty(n_rows * seq_per_img, dtype=torch.float32, device=dev)
+        stats = torch.empty(_lib.N_STATS, dtype=torch.float64, device=dev)
+        scratch = _scratch_for(dev, n_rows)
+        check(lib.cst_scb_apply(bcmr.data_ptr(), bcmr.data_ptr(), n_rows, seq_per_img, mode, k,
+                                reward.data_ptr(), stats.data_ptr(), scratch.data_ptr(),
+                                scratch.numel(), dev.index, _stream(dev)))
+    out = _finish(reward, stats, width)
+    return out + (stats,) if return_stats else out

@@ -1,0 +1,212 @@
+/*
+ * cst_reward.h -- C ABI of the B200 (sm_100a) CIDEr-D reward path.
+ *
+ * Drop-in boundary for the one hot path of AislingGui/cst_captioning: the
+ * CIDEr-D reward of the RL loop.  Every entry point names the reference
+ * interface it replaces (file:line under the reference checkout).
+ *
+ * Conventions
+ *   - plain C symbols, no exceptions cross the boundary;
+ *   - return value: 0 = OK, negative = error (CST_E_*); the message of the last
+ *     error on the calling thread is cst_last_error();
+ *   - the caller owns every buffer; the library owns only df-table handles;
+ *   - pointers marked [dev] are device pointers on the table's device, [host]
+ *     are host pointers;
+ *   - work is enqueued on the caller's stream (a cudaStream_t passed as void*,
+ *     NULL = legacy default stream) and the call returns WITHOUT synchronising,
+ *     except where a function says "synchronous";
+ *   - the product has no CPU fallback: without a CUDA device every compute entry
+ *     point fails with CST_E_CUDA.
+ *
+ * Token rows
+ *   A caption is a row of token ids (int32 or int64, row-major, `stride` elements
+ *   between rows).  Canonicalisation follows utils.py:135-152 (array_to_str):
+ *   the first 0 (<end>) ends the caption and is kept only if use_eos != 0; id 1
+ *   (<start>) is dropped wherever it occurs.  Rows may be at most 32 tokens wide
+ *   (reference: 30 for GT rows, <= 28 for sampled rows).  Ids must lie in
+ *   [0, 65534]; the id -1 is padding (it ends the caption and is never emitted,
+ *   whatever use_eos says).  Rows holding any other id are scored as if the bad
+ *   token ended the caption and are counted in stats[4].
+ *
+ * Packed n-gram keys
+ *   The n-gram (t0 .. t(k-1)), k = 1..4, is the 64-bit key
+ *       key = sum_i (t_i + 1) << (16 * i)
+ *   (a zero 16-bit lane means "no token", so <end> = id 0 stays representable).
+ *   This replaces the tuple-of-decimal-strings keys of compute_ciderdf.py:32,84.
+ */
+#ifndef CST_REWARD_H_
+#define CST_REWARD_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CST_OK 0
+#define CST_E_ARG (-1)     /* bad argument (NULL, size, range, mode) */
+#define CST_E_CUDA (-2)    /* CUDA runtime error, or no device */
+#define CST_E_NOMEM (-3)   /* host or device allocation failed */
+#define CST_E_RANGE (-4)   /* value outside what the kernels support */
+
+#define CST_DTYPE_I32 0
+#define CST_DTYPE_I64 1
+
+/* baseline modes of cst_reward / cst_scb_apply */
+#define CST_BASE_NONE 0        /* reward = score               (utils.py:317-319) */
+#define CST_BASE_GREEDY 1      /* reward = sampled - greedy    (utils.py:219-222) */
+#define CST_BASE_SCB_GT 2      /* scb_baseline == 1            (utils.py:296-300, 309-310) */
+#define CST_BASE_SCB_SAMPLE 3  /* scb_baseline == 2            (utils.py:301-304, 311-312) */
+
+#define CST_MAX_ROW_WIDTH 32
+#define CST_MAX_TOKEN_ID 65534
+#define CST_NGRAM_SLOTS_PER_ROW 128 /* 4 orders x 32 positions */
+#define CST_N_STATS 5
+
+typedef struct cst_df_table cst_df_table;
+
+/* Message of the last failing call on this thread ("" if none). */
+const char* cst_last_error(void);
+
+/* ABI version of the loaded library. */
+int cst_abi_version(void);
+
+/* ---- document-frequency table ------------------------------------------------
+ * Replaces the unpickled {'document_frequency': {ngram: df}, 'ref_len': n} dict
+ * that CiderD(df=path) holds (construction site train.py:121; pickle schema
+ * compute_ciderdf.py:123-129) with a device-resident open-addressing table
+ * keyed by packed n-grams.
+ *
+ * keys[n], df[n], idf[n] are [host].  idf[i] must be
+ *     log(n_documents) - log(max(1, df[i]))
+ * evaluated by the caller in float64 exactly as the scorer does (the Python
+ * wrapper uses numpy, so the values are bit-identical to the reference's);
+ * idf_unseen is the same expression for df = 0, i.e. log(n_documents).
+ * All idf must be >= 0 (df <= n_documents, which compute_ciderdf guarantees).
+ * Synchronous (one-off, like the pickle load it replaces). */
+int cst_df_create(const uint64_t* keys, const double* df, const double* idf,
+                  int64_t n, double idf_unseen, int device, cst_df_table** out);
+
+/* Build the table on the device from token rows: the device-side form of
+ * compute_ciderdf.py:56-93 (compute_doc_freq over per-video ref sets) and of the
+ * corpus-mode df the coco-caption scorer recomputes per call
+ * (compute_scores.py:92).  rows [dev] are canonicalised with `use_eos` like any
+ * other row; video v owns rows [video_offsets[v], video_offsets[v+1]) ([host],
+ * n_videos + 1 entries).  idf_by_df [host] has n_videos + 1 entries:
+ * idf_by_df[d] = log(n_videos) - log(max(1, d)) evaluated by the caller.
+ * Synchronous. */
+int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n_rows,
+                           int32_t width, int64_t stride,
+                           const int64_t* video_offsets, int64_t n_videos,
+                           int32_t use_eos, const double* idf_by_df, int device,
+                           cst_df_table** out);
+
+int cst_df_destroy(cst_df_table* table);
+
+/* Number of stored n-grams / slots / device of a table. */
+int64_t cst_df_size(const cst_df_table* table);
+int64_t cst_df_capacity(const cst_df_table* table);
+int cst_df_device(const cst_df_table* table);
+
+/* Copy the table's content back: keys_out[n], df_out[n] are [host], n =
+ * cst_df_size().  Order is unspecified.  Synchronous.  (Lets a device-built
+ * table be written as the reference's pickle, compute_ciderdf.py:123-129.) */
+int cst_df_export(const cst_df_table* table, uint64_t* keys_out, double* df_out);
+
+/* Parity probe: df_out[i] = document frequency of keys[i] (0.0 if absent),
+ * idf_out[i] its idf (idf_unseen if absent; may be NULL).  keys, df_out, idf_out
+ * are [dev].  The dict lookup it replaces is document_frequency[ngram] in the
+ * scorer's counts2vec. */
+int cst_df_lookup(const cst_df_table* table, const uint64_t* keys, int64_t n,
+                  double* df_out, double* idf_out, void* stream);
+
+/* ---- n-gram extraction probe ---------------------------------------------------
+ * Replaces array_to_str (utils.py:135-152) followed by precook
+ * (compute_ciderdf.py:19-34) for each row.  For row i the distinct n-grams are
+ * written to keys_out[i*128 ...] with their term frequencies in counts_out, in the
+ * insertion order of precook's dict (order 1..4 outer, first position inner);
+ * n_out[i] = how many, len_out[i] = canonical token count.  All outputs [dev].
+ * `device` selects the GPU (no table is involved). */
+int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows,
+                     int32_t width, int64_t stride, int32_t use_eos,
+                     uint64_t* keys_out, int32_t* counts_out, int32_t* n_out,
+                     int32_t* len_out, int device, void* stream);
+
+/* ---- scoring + reward ------------------------------------------------------------
+ * Replaces CiderD.compute_score(gts, res) as called from utils.py:208,274 together
+ * with the string building around it (utils.py:179-206, 249-272) and, for
+ * cst_reward, the baseline block (utils.py:219-224, 292-322).
+ *
+ *   cand        [dev] n_cand sampled rows (cand_width tokens, cand_stride apart)
+ *   greedy      [dev] n_cand greedy rows of the same geometry, or NULL
+ *               (required for CST_BASE_GREEDY; scored like utils.py:180-183)
+ *   refs        [dev] all reference rows, video-major
+ *   ref_offsets [dev] n_videos + 1 row offsets into refs (ragged ref counts), or
+ *               NULL when every video has exactly refs_per_video rows; with
+ *               ref_offsets, refs_per_video is the LARGEST ref count of any video
+ *               (it sizes the shared-memory staging; videos with more than 32
+ *               refs are staged in passes of 32)
+ *   cands_per_video   candidate i is scored against video i / cands_per_video:
+ *               seq_per_img for expand_feat == 1 (utils.py:266-270), 1 for
+ *               expand_feat == 0 (utils.py:271-272).  n_cand must equal
+ *               n_videos * cands_per_video.
+ *   scores_out  [dev] float64, n_cand entries (2 * n_cand when greedy != NULL:
+ *               sampled first, then greedy, the order of utils.py:180-183);
+ *               may be NULL in cst_reward.
+ */
+int cst_cider_scores(const cst_df_table* table,
+                     const void* cand, const void* greedy, int32_t cand_dtype,
+                     int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                     const void* refs, int32_t ref_dtype, int32_t ref_width,
+                     int64_t ref_stride, const int64_t* ref_offsets,
+                     int32_t refs_per_video, int64_t n_videos,
+                     int32_t cands_per_video, int32_t use_eos,
+                     double* scores_out, void* stream);
+
+/* Bytes of scratch cst_reward / cst_scb_apply need for n_groups baseline groups
+ * (for cst_reward: max(n_videos, n_cand / seq_per_img)).  The scratch buffer [dev] must be zero-filled once before its first
+ * use; the kernels leave it ready for the next call.  Calls sharing one scratch
+ * buffer must not overlap on the device. */
+int64_t cst_reward_scratch_bytes(int64_t n_groups);
+
+/* Scores + baseline in one launch.  seq_per_img is the row length of the
+ * reference's scores.reshape(-1, seq_per_img) (utils.py:284); the fused path needs
+ * cands_per_video == seq_per_img (expand_feat == 1, what train.py uses); for
+ * cands_per_video == 1 the baseline runs as a second small kernel over the scores.
+ *
+ *   mode        CST_BASE_*
+ *   scb_k       scb_captions (1..seq_per_img) for the two SCB modes
+ *   bcmrscores  [dev] float64 (n_cand / seq_per_img, seq_per_img) precomputed GT
+ *               consensus scores (dataloader.py:142-144), CST_BASE_SCB_GT only
+ *   reward_out  [dev] float32 n_cand: the column the reference repeats T times
+ *               (utils.py:224, 321-322) and casts to float (train.py:209)
+ *   stats_out   [dev] float64[CST_N_STATS] = { sum_m, sum_b, n_m, n_b, n_bad_rows }:
+ *               m_score = sum_m / n_m, b_score = sum_b / n_b as returned at
+ *               utils.py:226, 324 (sums, so ranks can all-reduce them);
+ *               n_bad_rows counts rows with ids outside [0, 65534].
+ */
+int cst_reward(const cst_df_table* table,
+               const void* cand, const void* greedy, int32_t cand_dtype,
+               int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+               const void* refs, int32_t ref_dtype, int32_t ref_width,
+               int64_t ref_stride, const int64_t* ref_offsets,
+               int32_t refs_per_video, int64_t n_videos,
+               int32_t cands_per_video, int32_t use_eos,
+               int32_t mode, int32_t seq_per_img, int32_t scb_k,
+               const double* bcmrscores,
+               float* reward_out, double* scores_out, double* stats_out,
+               void* scratch, int64_t scratch_bytes, void* stream);
+
+/* Baseline alone on given scores: utils.py:286-288 (WXE: scores are the
+ * precomputed consensus scores) and utils.py:292-322.  scores [dev] float64
+ * (n_rows, seq_per_img); for CST_BASE_GREEDY `other` holds the greedy scores, for
+ * CST_BASE_SCB_GT the bcmrscores; `device` selects the GPU. */
+int cst_scb_apply(const double* scores, const double* other, int64_t n_rows,
+                  int32_t seq_per_img, int32_t mode, int32_t scb_k,
+                  float* reward_out, double* stats_out, void* scratch,
+                  int64_t scratch_bytes, int device, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CST_REWARD_H_ */
