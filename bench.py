@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""Headline benchmark of the CIDEr-D reward path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU scorer, all host cores
+
+A "step" is one pass of the hot path over one batch: the CST_MS_SCB* workload of
+BASELINE.json configs[4] -- 65,536 synthetic videos x 20 sampled captions, each
+scored against the video's 20 references, SCB* baseline (scb_baseline=2,
+scb_captions=20, use_eos=1, expand_feat=1: the README recipe of the reference).
+One process per GPU; every rank owns its own 65,536 videos (weak scaling), the df
+table is replicated, and the only exchange is an all-reduce of the reward
+statistics.  Rank 0 prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = 'cider_d_reward_captions_per_sec_20refs'
+UNIT = 'captions/s'
+SEQ_PER_IMG = 20
+N_REFS = 20
+DF_VIDEOS = 6513
+CAND_W, REF_W = 28, 30
+# int32 candidate rows + int32 ref rows read once + fp32 reward written
+BYTES_PER_CAPTION = (4 * CAND_W * SEQ_PER_IMG + 4 * REF_W * N_REFS + 4 * SEQ_PER_IMG) / SEQ_PER_IMG
+
+
+def workload_config(n_videos, n_gpus):
+    return {
+        'workload': 'CST_MS_SCB* (BASELINE.json configs[4]): %d videos x %d sampled captions vs %d refs per GPU, '
+                    'SCB* baseline k=20, use_eos=1' % (n_videos, SEQ_PER_IMG, N_REFS),
+        'videos_per_gpu': n_videos, 'captions_per_step_per_gpu': n_videos * SEQ_PER_IMG,
+        'seq_per_img': SEQ_PER_IMG, 'refs_per_video': N_REFS, 'scb_baseline': 2, 'scb_captions': 20,
+        'df_corpus': '%dx%d synthetic captions, table built on device' % (DF_VIDEOS, N_REFS),
+        'parallelism': 'videos sharded, dp%d, df table replicated' % n_gpus,
+        'l2_policy': 'inputs (%.0f MB/step) exceed the 126 MB L2; no flush needed'
+                     % (n_videos * SEQ_PER_IMG * BYTES_PER_CAPTION / 1e6),
+    }
+
+
+# ---------------------------------------------------------------------------
+# clocks during the timed region
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x8: 'hw_slowdown', 0x40: 'hw_thermal_slowdown', 0x20: 'sw_thermal_slowdown',
+               0x4: 'sw_power_cap', 0x80: 'hw_power_brake_slowdown', 0x2: 'applications_clocks_setting'}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nv = None
+
+    def _run(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                for bit, name in self.REASONS.items():
+                    if bits & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.01)
+
+    def __enter__(self):
+        if self._nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': self.max_mhz, 'reasons': ['unavailable']}
+        return {'sm_mhz': float(np.median(self.samples)), 'sm_max_mhz': self.max_mhz,
+                'reasons': sorted(self.reasons), 'samples': len(self.samples)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    try:
+        return float(json.load(open(path))['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    except Exception:
+        return 6650.0, 'fallback (B200_PROFILING.md)'
+
+
+def ncu_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu capture."""
+    try:
+        return json.load(open(os.path.join(ROOT, 'profiles', 'roofline_traffic.json')))
+    except Exception:
+        return None
+
+
+# ---------------------------------------------------------------------------
+# CPU arms (oracle port; the reference itself is Python whose scorer is an absent
+# dependency, so there is no oracle/_ref to compile)
+# ---------------------------------------------------------------------------
+_CPU = {}
+
+
+def _cpu_init(df, n_doc):
+    from oracle import ciderd_oracle
+    _CPU['scorer'] = ciderd_oracle.CiderD(df=(df, n_doc))
+
+
+def _cpu_shard(args):
+    from oracle import reward_oracle
+    sampled, refs = args
+    gts = [refs[v].astype(np.int64) for v in range(refs.shape[0])]
+    rew, m, b = reward_oracle.get_cst_reward(sampled.astype(np.int64), gts, _CPU['scorer'], expand_feat=1,
+                                             seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1)
+    return float(rew[:, 0].sum())
+
+
+def cpu_df_dict():
+    """df of the bench corpus as the oracle's dict (vectorised: the Python
+    compute_doc_freq of the oracle takes ~8 s on this corpus and is not what is timed)."""
+    from cst_captioning_b200 import synth
+    from oracle import ciderd_oracle
+    rng = np.random.default_rng(synth.SEED)
+    refs, nw = synth.make_refs(rng, DF_VIDEOS, N_REFS)
+    df, n = ciderd_oracle.build_df_from_strings(synth.df_corpus_strings(refs, nw))
+    return df, n
+
+
+def run_cpu_sample(batch, n_videos, procs, df_pair):
+    """Oracle port of utils.get_cst_reward on the first n_videos of the batch -> seconds."""
+    sampled = batch['sampled'][:n_videos * SEQ_PER_IMG]
+    refs = batch['refs'][:n_videos]
+    if procs <= 1:
+        _cpu_init(*df_pair)
+        t0 = time.perf_counter()
+        _cpu_shard((sampled, refs))
+        return time.perf_counter() - t0
+    import multiprocessing as mp
+    bounds = np.linspace(0, n_videos, procs + 1).astype(int)
+    shards = [(sampled[a * SEQ_PER_IMG:b * SEQ_PER_IMG], refs[a:b]) for a, b in zip(bounds[:-1], bounds[1:]) if b > a]
+    with mp.get_context('fork').Pool(procs, initializer=_cpu_init, initargs=df_pair) as pool:
+        pool.map(_cpu_shard, [(s[:SEQ_PER_IMG], r[:1]) for s, r in shards])      # warm the workers
+        t0 = time.perf_counter()
+        pool.map(_cpu_shard, shards)
+        return time.perf_counter() - t0
+
+
+def reference_arm(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    from cst_captioning_b200 import synth
+    cores = os.cpu_count() or 1
+    df_pair = cpu_df_dict()
+    # size one step so that steps + warmup finish in about two minutes
+    probe_videos = max(cores, 8)
+    batch = synth.make_batch(max(4096, probe_videos), SEQ_PER_IMG, N_REFS, seed=1000)
+    t = run_cpu_sample(batch, probe_videos, cores, df_pair)
+    rate = probe_videos * SEQ_PER_IMG / t
+    budget = 120.0 / max(1, args.steps + args.warmup)
+    n_videos = int(min(4096, max(cores, rate * budget / SEQ_PER_IMG)))
+    for _ in range(args.warmup):
+        run_cpu_sample(batch, n_videos, cores, df_pair)
+    times = [run_cpu_sample(batch, n_videos, cores, df_pair) for _ in range(args.steps)]
+    total = float(np.sum(times))
+    value = n_videos * SEQ_PER_IMG * args.steps / total
+    sample = 'first %d videos (%d captions) of the step batch per step, %d worker processes' % (
+        n_videos, n_videos * SEQ_PER_IMG, cores)
+    line = {
+        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * total / args.steps,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': workload_config(args.videos, args.gpus),
+        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+        'note': 'oracle port of utils.get_cst_reward + restated CiderD (the scorer is an absent, unpinned '
+                'dependency of the reference; nothing to compile into oracle/_ref)',
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# the CUDA arm
+# ---------------------------------------------------------------------------
+def product_arm(args):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as graft
+    graft.build()
+    import cst_captioning_b200 as cst
+    from cst_captioning_b200 import synth
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device; the reward path has no CPU fallback')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+
+    # df table: built on the device from the 6513 x 20 corpus (words + <end>, use_eos=1)
+    rng = np.random.default_rng(synth.SEED)
+    corpus, _ = synth.make_refs(rng, DF_VIDEOS, N_REFS)
+    table = cst.DfTable.from_rows(torch.from_numpy(corpus).to(dev), use_eos=1)
+    scorer = cst.CiderD(df=table)
+
+    n_videos = args.videos
+    n_cap = n_videos * SEQ_PER_IMG
+    batch = synth.make_batch(n_videos, SEQ_PER_IMG, N_REFS, seed=1000 + rank)
+    h_cand = torch.from_numpy(batch['sampled']).pin_memory()
+    h_refs = torch.from_numpy(batch['refs']).pin_memory()
+    d_cand = h_cand.to(dev)
+    d_refs = cst.RefSet(h_refs.to(dev).reshape(n_videos * N_REFS, REF_W), per_video=N_REFS)
+    kw = dict(expand_feat=1, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1, return_stats=True)
+
+    def step():
+        rew, m, b, stats = cst.get_cst_reward(d_cand, d_refs, scorer, **kw)
+        if world > 1:
+            dist.all_reduce(stats)           # [sum_m, sum_b, n_m, n_b, bad]: the only exchange
+        return rew, stats
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- device-resident timing --------------------------------------------------
+    launches0 = cst.lib.cst_kernel_launches()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        barrier()
+        t_all0.record()
+        for a, b in ev:
+            a.record()
+            rew, stats = step()
+            b.record()
+        t_all1.record()
+        barrier()
+    launches = cst.lib.cst_kernel_launches() - launches0
+    total_ms = t_all0.elapsed_time(t_all1)
+    per_step = [a.elapsed_time(b) for a, b in ev]
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    stats = stats.cpu().numpy()
+    value = world * n_cap * args.steps / (total_ms * 1e-3)
+
+    # the dominant (only) kernel of a step is k_score: one launch per step, bracketed by events
+    kern_ms = float(np.mean(per_step)) if world == 1 else float(np.mean(per_step))
+    peak, peak_src = measured_peak()
+    achieved = n_cap * BYTES_PER_CAPTION / (kern_ms * 1e-3) / 1e9
+    traffic = ncu_traffic()
+    roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
+                'traffic': traffic['bytes_per_launch'] if traffic else None, 'kernel': 'k_score<int,int>',
+                'kernel_ms': kern_ms, 'bytes_per_caption': BYTES_PER_CAPTION, 'peak_source': peak_src,
+                'frac_of_nominal_8TBs': achieved / 8000.0}
+
+    # ---- end to end through the public API with HOST buffers -----------------------
+    e2e_steps = max(3, min(args.steps, 10))
+    out_pin = torch.empty(n_cap, dtype=torch.float32).pin_memory()
+    st_pin = torch.empty(5, dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        c = h_cand.to(dev, non_blocking=True)
+        r = h_refs.to(dev, non_blocking=True)
+        rew, m, b, st = cst.get_cst_reward(c, r, scorer, **kw)
+        if world > 1:
+            dist.all_reduce(st)
+        out_pin.copy_(rew[:, 0], non_blocking=True)
+        st_pin.copy_(st, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e = {'value': world * n_cap * e2e_steps / e2e_s, 'unit': UNIT,
+           'h2d_bytes_per_step': int(h_cand.numel() * 4 + h_refs.numel() * 4),
+           'd2h_bytes_per_step': int(out_pin.numel() * 4 + st_pin.numel() * 8), 'steps': e2e_steps,
+           'ms_per_step': 1e3 * e2e_s / e2e_steps}
+
+    # ---- CPU baseline: oracle port, one core, bounded sample (rank 0, N = 1 only) --
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        n_s = args.cpu_videos
+        secs = run_cpu_sample(batch, n_s, 1, cpu_df_dict())
+        cpu = {'value': n_s * SEQ_PER_IMG / secs, 'unit': UNIT, 'cores': 1, 'kind': 'port',
+               'sample': 'first %d videos (%d captions) of the step batch, oracle port of utils.get_cst_reward '
+                         '+ restated CiderD, %.1f s' % (n_s, n_s * SEQ_PER_IMG, secs),
+               'host_cores_available': os.cpu_count()}
+
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps,
+            'warmup': max(args.warmup, 3), 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': workload_config(n_videos, world), 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e,
+            'gpu_launches': int(launches), 'clocks': clocks.summary(),
+            'check': {'m_score': float(stats[0] / stats[2]), 'b_score': float(stats[1] / stats[3]),
+                      'bad_rows': float(stats[4]), 'df_ngrams': len(table)},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--videos', type=int, default=65536, help='videos per GPU per step')
+    ap.add_argument('--cpu-videos', type=int, default=160, help='CPU-baseline sample size (videos)')
+    ap.add_argument('--no-cpu', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        return reference_arm(args)
+    return product_arm(args)
+
+
+if __name__ == '__main__':
+    sys.exit(main())

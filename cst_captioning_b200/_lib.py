@@ -27,7 +27,8 @@ _ROWS = [_vp, _vp, _i32, _i64, _i32, _i64,      # cand, greedy, dtype, n_cand, w
 SYMBOLS = {
     'cst_last_error': (C.c_char_p, []),
     'cst_abi_version': (C.c_int, []),
-    'cst_df_create': (C.c_int, [_vp, _vp, _vp, _i64, _f64, C.c_int, C.POINTER(_vp)]),
+    'cst_kernel_launches': (_i64, []),
+    'cst_df_create': (C.c_int, [_vp, _vp, _i64, _vp, _i64, C.c_int, C.POINTER(_vp)]),
     'cst_df_build_from_rows': (C.c_int, [_vp, _i32, _i64, _i32, _i64, _vp, _i64, _i32, _vp, C.c_int,
                                          C.POINTER(_vp)]),
     'cst_df_destroy': (C.c_int, [_vp]),

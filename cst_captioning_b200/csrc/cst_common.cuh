@@ -16,12 +16,26 @@ typedef unsigned int u32;
 #define CST_GAUSS_N (2 * CST_GAUSS_HALF + 1)
 
 // ---------------------------------------------------------------------------
-// global df table: open addressing, linear probing, 16-byte slots so that one
-// LDG.128 fetches key and idf together.
+// global df table (HBM, meant to stay L2-resident)
+//
+//   keys     [n_buckets][4] u64   open addressing over 32-byte buckets: one
+//                                 256-bit load (one L2 sector) fetches a whole
+//                                 bucket; a bucket with an empty slot ends a probe
+//   dfc      [n_buckets][4] u32   document frequency of the key in the same slot
+//   lut      [n_documents + 1]    idf by document frequency, float64 computed by the
+//                                 caller (bit-identical to the scorer's numpy value)
+//   uni      [CST_UNI_N] f64      idf of unigram `token` directly (no hashing)
 // ---------------------------------------------------------------------------
-struct __align__(16) DfSlot {
-    u64 key;      // 0 = empty
-    double idf;   // log(n_documents) - log(max(1, df)), computed by the caller in float64
+#define CST_BUCKET 4
+#define CST_UNI_N 65535
+
+struct DfView {
+    const u64* keys;
+    const u32* dfc;
+    const double* lut;
+    const double* uni;
+    u32 n_buckets;
+    double unseen;   // idf of an n-gram absent from the table = lut[0]
 };
 
 // Fibonacci hash: bits 32..63 of key * phi.  Both tables (global df table,
@@ -36,38 +50,50 @@ __host__ __device__ __forceinline__ u32 cst_slot(u32 h, u32 cap) {
 
 #ifdef __CUDACC__
 
-__device__ __forceinline__ ulonglong2 ld_slot(const DfSlot* p) {
-    return __ldg(reinterpret_cast<const ulonglong2*>(p));
+// One bucket = 4 keys = 32 bytes = one sector, fetched by a single LDG.256.
+__device__ __forceinline__ void ld_bucket(const u64* p, u64 k[4]) {
+    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+                 : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3])
+                 : "l"(p));
 }
 
-// idf of up to four keys per lane, first probes issued back to back so the four
-// L2 round trips overlap.  Lanes/orders with need[k] == false cost one load of
-// slot 0 (hot in L1) and get `unseen`.
-__device__ __forceinline__ void df_probe4(const DfSlot* __restrict__ tab, u32 cap, double unseen,
-                                          const u64 key[4], const u32 h[4], const bool need[4],
+// slot index of `key` (>= 0), or -1 if absent.  `b` is the home bucket, `k` its
+// already loaded keys.  Overflow into the next bucket is rare (load factor 0.5).
+__device__ __forceinline__ int bucket_resolve(const u64* __restrict__ keys, u32 nb, u32 b, u64 k[4], u64 key) {
+    for (;;) {
+#pragma unroll
+        for (int j = 0; j < CST_BUCKET; ++j)
+            if (k[j] == key) return (int)(b * CST_BUCKET + j);
+        if (k[3] == 0ull) return -1;          // slots fill front to back: an empty tail ends the probe
+        b = (b + 1 == nb) ? 0u : b + 1;
+        ld_bucket(keys + (size_t)b * CST_BUCKET, k);
+    }
+}
+
+// idf of the four n-grams of a lane.  Order 1 is a direct load; the bucket loads of
+// orders 2..4 are issued back to back so their L2 round trips overlap, then the
+// df loads, then the (L1-resident) idf LUT loads.
+__device__ __forceinline__ void df_probe4(const DfView& t, const u64 key[4], const u32 h[4], const bool need[4],
                                           double idf[4]) {
-    u32 s[4];
-    ulonglong2 v[4];
+    const u32 tok = (u32)key[0] - 1u;
+    double w0 = t.unseen;
+    if (need[0] && tok < CST_UNI_N) w0 = __ldg(t.uni + tok);
+    u32 b[4];
+    u64 kk[4][4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        s[k] = need[k] ? cst_slot(h[k], cap) : 0u;
-        v[k] = ld_slot(tab + s[k]);
+    for (int k = 1; k < 4; ++k) {
+        b[k] = need[k] ? cst_slot(h[k], t.n_buckets) : 0u;
+        ld_bucket(t.keys + (size_t)b[k] * CST_BUCKET, kk[k]);
     }
+    int slot[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        double r = unseen;
-        if (need[k]) {
-            ulonglong2 x = v[k];
-            u32 q = s[k];
-            for (;;) {
-                if (x.x == key[k]) { r = __longlong_as_double((long long)x.y); break; }
-                if (x.x == 0ull) break;
-                q = (q + 1 == cap) ? 0u : q + 1;
-                x = ld_slot(tab + q);
-            }
-        }
-        idf[k] = r;
-    }
+    for (int k = 1; k < 4; ++k) slot[k] = need[k] ? bucket_resolve(t.keys, t.n_buckets, b[k], kk[k], key[k]) : -1;
+    u32 d[4];
+#pragma unroll
+    for (int k = 1; k < 4; ++k) d[k] = (slot[k] >= 0) ? __ldg(t.dfc + slot[k]) : 0u;
+    idf[0] = w0;
+#pragma unroll
+    for (int k = 1; k < 4; ++k) idf[k] = (slot[k] >= 0) ? __ldg(t.lut + d[k]) : t.unseen;
 }
 
 __device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u; }
@@ -85,7 +111,7 @@ template <typename T>
 __device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, int use_eos,
                                           int lane, u32* tokbuf, u64 key[4], int& L) {
     const bool in = lane < width;
-    long long t = in ? (long long)row[lane] : 0ll;
+    long long t = in ? (long long)__ldcs(row + lane) : 0ll;   // rows stream through once: evict-first
     const bool bad = in && (t < -1 || t > 65534);
     const bool term = in && (t == 0 || t == -1 || bad);   // -1 = padding: ends the row, never emitted
     const u32 tmask = __ballot_sync(CST_FULL, term);
@@ -154,7 +180,7 @@ __device__ __forceinline__ double warp_sum4_transposed(const double v[4], int la
 __device__ __forceinline__ int lane_order(int lane) { return ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1); }
 
 __device__ __forceinline__ double inv_norm_of(double sumsq) {
-    return sumsq > 0.0 ? 1.0 / sqrt(sumsq) : 0.0;
+    return sumsq > 0.0 ? rsqrt(sumsq) : 0.0;
 }
 
 // ---------------------------------------------------------------------------

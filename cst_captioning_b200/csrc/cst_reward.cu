@@ -17,6 +17,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <new>
 #include <vector>
 
@@ -46,6 +47,11 @@ static int fail(int code, const char* fmt, ...) {
 extern "C" const char* cst_last_error(void) { return g_err; }
 extern "C" int cst_abi_version(void) { return 1; }
 
+// every kernel this library launches is counted here (bench.py reports it)
+static std::atomic<long long> g_launches{0};
+#define COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
+extern "C" int64_t cst_kernel_launches(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
+
 struct DeviceGuard {
     int prev = -1;
     bool ok = false;
@@ -59,22 +65,36 @@ struct DeviceGuard {
 };
 
 // ---------------------------------------------------------------------------
-// df table handle
+// df table handle (layout: DfView in cst_common.cuh)
 // ---------------------------------------------------------------------------
 struct cst_df_table {
     int device;
-    u32 capacity;
+    u32 n_buckets;
     int64_t size;
+    int64_t n_documents;
     double idf_unseen;
-    DfSlot* slots;   // [capacity]  hot: key + idf, one LDG.128 per probe
-    double* df;      // [capacity]  cold: raw document frequency (parity probe / export)
+    u64* keys;       // [n_buckets * 4]
+    u32* dfc;        // [n_buckets * 4]
+    double* lut;     // [n_documents + 1]
+    double* uni;     // [CST_UNI_N]
     double* gauss;   // [CST_GAUSS_N] e^{-d^2 / (2 sigma^2)}, d = index - CST_GAUSS_HALF
 };
 
-static u32 df_capacity_for(int64_t n) {
-    int64_t cap = 2 * n + 16;   // load factor <= 0.5
-    if (cap < 1024) cap = 1024;
-    return (u32)cap;
+static DfView view_of(const cst_df_table* t) {
+    DfView v;
+    v.keys = t->keys;
+    v.dfc = t->dfc;
+    v.lut = t->lut;
+    v.uni = t->uni;
+    v.n_buckets = t->n_buckets;
+    v.unseen = t->idf_unseen;
+    return v;
+}
+
+static u32 df_buckets_for(int64_t n) {
+    int64_t nb = (2 * n + CST_BUCKET - 1) / CST_BUCKET + 4;   // load factor <= 0.5
+    if (nb < 256) nb = 256;
+    return (u32)nb;
 }
 
 // Gaussian length penalty exactly as the scorer evaluates it:
@@ -87,25 +107,33 @@ static void fill_gauss(double* g) {
     }
 }
 
-static int table_alloc(int device, u32 cap, double idf_unseen, cst_df_table** out) {
+// Allocate a zeroed table and upload the idf LUT (idf_by_df: n_documents + 1 values).
+static int table_alloc(int device, u32 n_buckets, const double* idf_by_df, int64_t n_documents,
+                       cst_df_table** out) {
     cst_df_table* t = new (std::nothrow) cst_df_table();
     if (!t) return fail(CST_E_NOMEM, "out of host memory");
+    memset(t, 0, sizeof(*t));
     t->device = device;
-    t->capacity = cap;
-    t->size = 0;
-    t->idf_unseen = idf_unseen;
-    t->slots = nullptr;
-    t->df = nullptr;
-    t->gauss = nullptr;
+    t->n_buckets = n_buckets;
+    t->n_documents = n_documents;
+    t->idf_unseen = idf_by_df[0];
     double g[CST_GAUSS_N];
     fill_gauss(g);
-    cudaError_t e = cudaMalloc(&t->slots, (size_t)cap * sizeof(DfSlot));
-    if (e == cudaSuccess) e = cudaMalloc(&t->df, (size_t)cap * sizeof(double));
+    const size_t slots = (size_t)n_buckets * CST_BUCKET;
+    cudaError_t e = cudaMalloc(&t->keys, slots * sizeof(u64));
+    if (e == cudaSuccess) e = cudaMalloc(&t->dfc, slots * sizeof(u32));
+    if (e == cudaSuccess) e = cudaMalloc(&t->lut, (size_t)(n_documents + 1) * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&t->uni, (size_t)CST_UNI_N * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&t->gauss, sizeof(g));
+    if (e == cudaSuccess) e = cudaMemset(t->keys, 0, slots * sizeof(u64));
+    if (e == cudaSuccess) e = cudaMemset(t->dfc, 0, slots * sizeof(u32));
+    if (e == cudaSuccess) e = cudaMemcpy(t->lut, idf_by_df, (size_t)(n_documents + 1) * sizeof(double), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(t->gauss, g, sizeof(g), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
-        cudaFree(t->slots);
-        cudaFree(t->df);
+        cudaFree(t->keys);
+        cudaFree(t->dfc);
+        cudaFree(t->lut);
+        cudaFree(t->uni);
         cudaFree(t->gauss);
         delete t;
         return fail(e == cudaErrorMemoryAllocation ? CST_E_NOMEM : CST_E_CUDA, "df table allocation: %s",
@@ -115,50 +143,93 @@ static int table_alloc(int device, u32 cap, double idf_unseen, cst_df_table** ou
     return CST_OK;
 }
 
-extern "C" int cst_df_create(const uint64_t* keys, const double* df, const double* idf, int64_t n,
-                             double idf_unseen, int device, cst_df_table** out) {
+// uni[token] = idf of the unigram `token` (direct-indexed shortcut of the hash table)
+__global__ void k_fill_uni(DfView t, double* uni) {
+    const u32 tok = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tok >= CST_UNI_N) return;
+    const u64 key = (u64)tok + 1ull;
+    u64 k[4];
+    const u32 b = cst_slot(cst_hash(key), t.n_buckets);
+    ld_bucket(t.keys + (size_t)b * CST_BUCKET, k);
+    const int slot = bucket_resolve(t.keys, t.n_buckets, b, k, key);
+    uni[tok] = (slot >= 0) ? t.lut[t.dfc[slot]] : t.unseen;
+}
+
+static int table_finish(cst_df_table* t) {
+    k_fill_uni<<<(CST_UNI_N + 255) / 256, 256>>>(view_of(t), t->uni);
+    COUNT_LAUNCH();
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaDeviceSynchronize());
+    return CST_OK;
+}
+
+static int check_lut(const char* who, const double* idf_by_df, int64_t n_documents) {
+    if (!idf_by_df || n_documents < 1) return fail(CST_E_ARG, "%s: idf_by_df / n_documents missing", who);
+    if (n_documents > (int64_t)1 << 28) return fail(CST_E_RANGE, "%s: n_documents too large", who);
+    for (int64_t d = 0; d <= n_documents; ++d)
+        if (!(idf_by_df[d] >= 0.0)) return fail(CST_E_ARG, "%s: idf_by_df[%lld] is negative or NaN", who, (long long)d);
+    return CST_OK;
+}
+
+extern "C" int cst_df_create(const uint64_t* keys, const double* df, int64_t n, const double* idf_by_df,
+                             int64_t n_documents, int device, cst_df_table** out) {
     if (!out) return fail(CST_E_ARG, "cst_df_create: out is NULL");
     *out = nullptr;
-    if (n < 0 || (n > 0 && (!keys || !df || !idf))) return fail(CST_E_ARG, "cst_df_create: NULL input");
+    if (n < 0 || (n > 0 && (!keys || !df))) return fail(CST_E_ARG, "cst_df_create: NULL input");
     if (n > (int64_t)1 << 30) return fail(CST_E_RANGE, "cst_df_create: %lld n-grams exceed 2^30", (long long)n);
-    if (!(idf_unseen >= 0.0)) return fail(CST_E_ARG, "cst_df_create: idf_unseen must be >= 0");
+    int rc = check_lut("cst_df_create", idf_by_df, n_documents);
+    if (rc != CST_OK) return rc;
     DeviceGuard guard(device);
     if (!guard.ok) return fail(CST_E_CUDA, "cst_df_create: cannot select CUDA device %d", device);
 
-    const u32 cap = df_capacity_for(n);
-    std::vector<DfSlot> h_slots;
-    std::vector<double> h_df;
+    const u32 nb = df_buckets_for(n);
+    const size_t slots = (size_t)nb * CST_BUCKET;
+    std::vector<u64> h_keys;
+    std::vector<u32> h_dfc;
     try {
-        h_slots.assign(cap, DfSlot{0ull, 0.0});
-        h_df.assign(cap, 0.0);
+        h_keys.assign(slots, 0ull);
+        h_dfc.assign(slots, 0u);
     } catch (const std::bad_alloc&) {
-        return fail(CST_E_NOMEM, "cst_df_create: out of host memory for %u slots", cap);
+        return fail(CST_E_NOMEM, "cst_df_create: out of host memory for %zu slots", slots);
     }
     for (int64_t i = 0; i < n; ++i) {
         const u64 k = keys[i];
         if (k == 0ull || (k & 0xffffull) == 0ull)
             return fail(CST_E_ARG, "cst_df_create: key %lld is not a packed n-gram", (long long)i);
-        if (!(idf[i] >= 0.0))
-            return fail(CST_E_ARG, "cst_df_create: idf[%lld] < 0 (df exceeds the document count)", (long long)i);
-        u32 s = cst_slot(cst_hash(k), cap);
-        while (h_slots[s].key != 0ull) {
-            if (h_slots[s].key == k) return fail(CST_E_ARG, "cst_df_create: duplicate key at %lld", (long long)i);
-            s = (s + 1 == cap) ? 0u : s + 1;
+        const double d = df[i];
+        if (!(d >= 0.0) || d > (double)n_documents || d != floor(d))
+            return fail(CST_E_ARG, "cst_df_create: df[%lld] = %g is not an integer in [0, n_documents]", (long long)i, d);
+        u32 b = cst_slot(cst_hash(k), nb);
+        for (;;) {
+            int j = 0;
+            for (; j < CST_BUCKET; ++j) {
+                u64 cur = h_keys[(size_t)b * CST_BUCKET + j];
+                if (cur == k) return fail(CST_E_ARG, "cst_df_create: duplicate key at %lld", (long long)i);
+                if (cur == 0ull) break;
+            }
+            if (j < CST_BUCKET) {
+                h_keys[(size_t)b * CST_BUCKET + j] = k;
+                h_dfc[(size_t)b * CST_BUCKET + j] = (u32)d;
+                break;
+            }
+            b = (b + 1 == nb) ? 0u : b + 1;
         }
-        h_slots[s].key = k;
-        h_slots[s].idf = idf[i];
-        h_df[s] = df[i];
     }
     cst_df_table* t = nullptr;
-    int rc = table_alloc(device, cap, idf_unseen, &t);
+    rc = table_alloc(device, nb, idf_by_df, n_documents, &t);
     if (rc != CST_OK) return rc;
-    cudaError_t e = cudaMemcpy(t->slots, h_slots.data(), (size_t)cap * sizeof(DfSlot), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(t->df, h_df.data(), (size_t)cap * sizeof(double), cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMemcpy(t->keys, h_keys.data(), slots * sizeof(u64), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(t->dfc, h_dfc.data(), slots * sizeof(u32), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
         cst_df_destroy(t);
         return fail(CST_E_CUDA, "cst_df_create: upload failed: %s", cudaGetErrorString(e));
     }
     t->size = n;
+    rc = table_finish(t);
+    if (rc != CST_OK) {
+        cst_df_destroy(t);
+        return rc;
+    }
     *out = t;
     return CST_OK;
 }
@@ -166,31 +237,34 @@ extern "C" int cst_df_create(const uint64_t* keys, const double* df, const doubl
 extern "C" int cst_df_destroy(cst_df_table* t) {
     if (!t) return CST_OK;
     DeviceGuard guard(t->device);
-    cudaFree(t->slots);
-    cudaFree(t->df);
+    cudaFree(t->keys);
+    cudaFree(t->dfc);
+    cudaFree(t->lut);
+    cudaFree(t->uni);
     cudaFree(t->gauss);
     delete t;
     return CST_OK;
 }
 
 extern "C" int64_t cst_df_size(const cst_df_table* t) { return t ? t->size : -1; }
-extern "C" int64_t cst_df_capacity(const cst_df_table* t) { return t ? (int64_t)t->capacity : -1; }
+extern "C" int64_t cst_df_capacity(const cst_df_table* t) { return t ? (int64_t)t->n_buckets * CST_BUCKET : -1; }
 extern "C" int cst_df_device(const cst_df_table* t) { return t ? t->device : -1; }
 
 extern "C" int cst_df_export(const cst_df_table* t, uint64_t* keys_out, double* df_out) {
     if (!t || (t->size > 0 && (!keys_out || !df_out))) return fail(CST_E_ARG, "cst_df_export: NULL argument");
     DeviceGuard guard(t->device);
     if (!guard.ok) return fail(CST_E_CUDA, "cst_df_export: cannot select device %d", t->device);
-    std::vector<DfSlot> h_slots(t->capacity);
-    std::vector<double> h_df(t->capacity);
-    CUDA_TRY(cudaMemcpy(h_slots.data(), t->slots, (size_t)t->capacity * sizeof(DfSlot), cudaMemcpyDeviceToHost));
-    CUDA_TRY(cudaMemcpy(h_df.data(), t->df, (size_t)t->capacity * sizeof(double), cudaMemcpyDeviceToHost));
+    const size_t slots = (size_t)t->n_buckets * CST_BUCKET;
+    std::vector<u64> h_keys(slots);
+    std::vector<u32> h_dfc(slots);
+    CUDA_TRY(cudaMemcpy(h_keys.data(), t->keys, slots * sizeof(u64), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(h_dfc.data(), t->dfc, slots * sizeof(u32), cudaMemcpyDeviceToHost));
     int64_t at = 0;
-    for (u32 s = 0; s < t->capacity; ++s) {
-        if (h_slots[s].key == 0ull) continue;
+    for (size_t s = 0; s < slots; ++s) {
+        if (h_keys[s] == 0ull) continue;
         if (at >= t->size) return fail(CST_E_CUDA, "cst_df_export: table holds more keys than its size");
-        keys_out[at] = h_slots[s].key;
-        df_out[at] = h_df[s];
+        keys_out[at] = h_keys[s];
+        df_out[at] = (double)h_dfc[s];
         ++at;
     }
     if (at != t->size) return fail(CST_E_CUDA, "cst_df_export: found %lld keys, expected %lld", (long long)at, (long long)t->size);
@@ -200,21 +274,24 @@ extern "C" int cst_df_export(const cst_df_table* t, uint64_t* keys_out, double* 
 // ---------------------------------------------------------------------------
 // parity probes
 // ---------------------------------------------------------------------------
-__global__ void k_df_lookup(const DfSlot* __restrict__ tab, const double* __restrict__ dfv, u32 cap,
-                            double unseen, const u64* __restrict__ keys, int64_t n, double* df_out,
-                            double* idf_out) {
+// Looks keys up exactly the way the scoring kernels do: unigram idf through the
+// direct array, everything else through the bucketed table + LUT.
+__global__ void k_df_lookup(DfView t, const u64* __restrict__ keys, int64_t n, double* df_out, double* idf_out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const u64 key = keys[i];
-    double d = 0.0, w = unseen;
+    double d = 0.0, w = t.unseen;
     if (key != 0ull) {
-        u32 s = cst_slot(cst_hash(key), cap);
-        for (;;) {
-            ulonglong2 x = ld_slot(tab + s);
-            if (x.x == key) { d = dfv[s]; w = __longlong_as_double((long long)x.y); break; }
-            if (x.x == 0ull) break;
-            s = (s + 1 == cap) ? 0u : s + 1;
+        u64 k[4];
+        const u32 b = cst_slot(cst_hash(key), t.n_buckets);
+        ld_bucket(t.keys + (size_t)b * CST_BUCKET, k);
+        const int slot = bucket_resolve(t.keys, t.n_buckets, b, k, key);
+        if (slot >= 0) {
+            const u32 c = t.dfc[slot];
+            d = (double)c;
+            w = t.lut[c];
         }
+        if ((key >> 16) == 0ull && (u32)key - 1u < CST_UNI_N) w = t.uni[(u32)key - 1u];
     }
     df_out[i] = d;
     if (idf_out) idf_out[i] = w;
@@ -228,8 +305,8 @@ extern "C" int cst_df_lookup(const cst_df_table* t, const uint64_t* keys, int64_
     if (!guard.ok) return fail(CST_E_CUDA, "cst_df_lookup: cannot select device %d", t->device);
     const int threads = 256;
     const int64_t blocks = (n + threads - 1) / threads;
-    k_df_lookup<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(
-        t->slots, t->df, t->capacity, t->idf_unseen, (const u64*)keys, n, df_out, idf_out);
+    k_df_lookup<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(view_of(t), (const u64*)keys, n, df_out, idf_out);
+    COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
 }
@@ -285,6 +362,7 @@ extern "C" int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows,
     else
         k_ngram_counts<int64_t><<<blocks, 256, 0, st>>>((const int64_t*)rows, n_rows, width, stride, use_eos,
                                                        (u64*)keys_out, counts_out, n_out, len_out);
+    COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
 }
@@ -396,9 +474,7 @@ __device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* parti
 // fused scoring kernel
 // ---------------------------------------------------------------------------
 struct ScoreParams {
-    const DfSlot* df;
-    u32 df_cap;
-    double idf_unseen;
+    DfView df;
     const double* gauss;
     const void* cand;
     const void* greedy;
@@ -443,7 +519,7 @@ __device__ __forceinline__ bool ref_phase(const ScoreParams& p, const RT* row, i
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
     double idf[4];
-    df_probe4(p.df, p.df_cap, p.idf_unseen, key, h, lead, idf);
+    df_probe4(p.df, key, h, lead, idf);
 
     const u32 mask = p.tab_slots - 1u;
     const u32 bit = 1u << rl;
@@ -488,7 +564,7 @@ __device__ __forceinline__ double cand_phase(const ScoreParams& p, const CT* row
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
     double idf[4];
-    df_probe4(p.df, p.df_cap, p.idf_unseen, key, h, lead, idf);
+    df_probe4(p.df, key, h, lead, idf);
 
     // Gaussian length penalty against every ref of the chunk
     const int lenh = (L > 1) ? (L - 1) : 0;
@@ -540,7 +616,7 @@ __device__ __forceinline__ double cand_phase(const ScoreParams& p, const CT* row
 }
 
 template <typename CT, typename RT>
-__global__ void __launch_bounds__(CST_MAX_WARPS * 32) k_score(const ScoreParams p) {
+__global__ void __launch_bounds__(CST_MAX_WARPS * 32, 2) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -690,6 +766,7 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
     }
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
     k_score<CT, RT><<<grid, threads, smem, st>>>(p);
+    COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
 }
@@ -727,9 +804,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
 
     ScoreParams p;
     memset(&p, 0, sizeof(p));
-    p.df = t->slots;
-    p.df_cap = t->capacity;
-    p.idf_unseen = t->idf_unseen;
+    p.df = view_of(t);
     p.gauss = t->gauss;
     p.cand = cand;
     p.greedy = greedy;
@@ -829,6 +904,7 @@ extern "C" int cst_scb_apply(const double* scores, const double* other, int64_t 
     k_scb<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
         scores, other, n_rows, seq_per_img, mode, scb_k, reward_out, stats_out, reinterpret_cast<u32*>(scratch),
         reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256), n_m, n_b);
+    COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
 }
@@ -927,23 +1003,25 @@ __global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, in
     }
 }
 
-// Move the counted keys into the final table (own capacity), idf looked up from
-// the caller's float64 LUT so it is bit-identical to the scorer's numpy value.
-__global__ void k_df_rehash(const u64* __restrict__ g_keys, const u32* __restrict__ g_cnt, u32 g_cap,
-                            const double* __restrict__ idf_by_df, DfSlot* slots, double* df, u32 cap) {
+// Move the counted keys into the final bucketed table.  Slots of a bucket fill front
+// to back (the lookup relies on it: an empty last slot ends a probe).
+__global__ void k_df_rehash(const u64* __restrict__ g_keys, const u32* __restrict__ g_cnt, u32 g_cap, u64* keys,
+                            u32* dfc, u32 n_buckets) {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g_cap) return;
     const u64 key = g_keys[i];
     if (key == 0ull) return;
-    const u32 c = g_cnt[i];
-    u32 s = cst_slot(cst_hash(key), cap);
+    u32 b = cst_slot(cst_hash(key), n_buckets);
     for (;;) {
-        u64 old = atomicCAS(reinterpret_cast<u64*>(&slots[s].key), 0ull, key);
-        if (old == 0ull) break;
-        s = (s + 1 == cap) ? 0u : s + 1;
+        for (int j = 0; j < CST_BUCKET; ++j) {
+            const size_t s = (size_t)b * CST_BUCKET + j;
+            if (atomicCAS(&keys[s], 0ull, key) == 0ull) {
+                dfc[s] = g_cnt[i];
+                return;
+            }
+        }
+        b = (b + 1 == n_buckets) ? 0u : b + 1;
     }
-    slots[s].idf = idf_by_df[c];
-    df[s] = (double)c;
 }
 
 extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n_rows, int32_t width,
@@ -951,8 +1029,12 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
                                       int32_t use_eos, const double* idf_by_df, int device, cst_df_table** out) {
     if (!out) return fail(CST_E_ARG, "cst_df_build_from_rows: out is NULL");
     *out = nullptr;
-    if (n_rows < 0 || n_videos < 1 || !video_offsets || !idf_by_df || (n_rows > 0 && !rows))
+    if (n_rows < 0 || n_videos < 1 || !video_offsets || (n_rows > 0 && !rows))
         return fail(CST_E_ARG, "cst_df_build_from_rows: bad argument");
+    {
+        int lrc = check_lut("cst_df_build_from_rows", idf_by_df, n_videos);
+        if (lrc != CST_OK) return lrc;
+    }
     if (width < 1 || width > CST_MAX_ROW_WIDTH)
         return fail(CST_E_RANGE, "cst_df_build_from_rows: row width %d outside [1, %d]", width, CST_MAX_ROW_WIDTH);
     if (stride < width) return fail(CST_E_ARG, "cst_df_build_from_rows: stride < width");
@@ -985,7 +1067,6 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     u32* g_cnt = nullptr;
     u32* counters = nullptr;      // [0] unique keys, [1] bad rows
     int64_t* d_off = nullptr;
-    double* d_lut = nullptr;
     cst_df_table* t = nullptr;
     int rc = CST_OK;
     cudaError_t e = cudaSuccess;
@@ -1005,12 +1086,10 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     BUILD_TRY(cudaMalloc(&g_cnt, (size_t)g_cap * sizeof(u32)));
     BUILD_TRY(cudaMalloc(&counters, 2 * sizeof(u32)));
     BUILD_TRY(cudaMalloc(&d_off, (size_t)(n_videos + 1) * sizeof(int64_t)));
-    BUILD_TRY(cudaMalloc(&d_lut, (size_t)(n_videos + 1) * sizeof(double)));
     BUILD_TRY(cudaMemset(g_keys, 0, (size_t)g_cap * sizeof(u64)));
     BUILD_TRY(cudaMemset(g_cnt, 0, (size_t)g_cap * sizeof(u32)));
     BUILD_TRY(cudaMemset(counters, 0, 2 * sizeof(u32)));
     BUILD_TRY(cudaMemcpy(d_off, video_offsets, (size_t)(n_videos + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
-    BUILD_TRY(cudaMemcpy(d_lut, idf_by_df, (size_t)(n_videos + 1) * sizeof(double), cudaMemcpyHostToDevice));
     if (dtype == CST_DTYPE_I32) {
         BUILD_TRY(cudaFuncSetAttribute(k_df_build<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_df_build<int32_t><<<grid, 256, smem>>>((const int32_t*)rows, width, stride, use_eos ? 1 : 0, d_off,
@@ -1022,6 +1101,7 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
                                                  n_videos, set_slots, set_shift, g_keys, g_cnt, g_cap, counters,
                                                  counters + 1);
     }
+    COUNT_LAUNCH();
     BUILD_TRY(cudaGetLastError());
     BUILD_TRY(cudaMemcpy(h_counters, counters, sizeof(h_counters), cudaMemcpyDeviceToHost));
     if (h_counters[1] != 0) {
@@ -1029,21 +1109,21 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
                   CST_MAX_TOKEN_ID);
         goto done;
     }
-    rc = table_alloc(device, df_capacity_for((int64_t)h_counters[0]), idf_by_df[0], &t);
+    rc = table_alloc(device, df_buckets_for((int64_t)h_counters[0]), idf_by_df, n_videos, &t);
     if (rc != CST_OK) goto done;
-    BUILD_TRY(cudaMemset(t->slots, 0, (size_t)t->capacity * sizeof(DfSlot)));
-    BUILD_TRY(cudaMemset(t->df, 0, (size_t)t->capacity * sizeof(double)));
-    k_df_rehash<<<(g_cap + 255) / 256, 256>>>(g_keys, g_cnt, g_cap, d_lut, t->slots, t->df, t->capacity);
+    k_df_rehash<<<(g_cap + 255) / 256, 256>>>(g_keys, g_cnt, g_cap, t->keys, t->dfc, t->n_buckets);
+    COUNT_LAUNCH();
     BUILD_TRY(cudaGetLastError());
     BUILD_TRY(cudaDeviceSynchronize());
     t->size = (int64_t)h_counters[0];
+    rc = table_finish(t);
+    if (rc != CST_OK) goto done;
 done:
 #undef BUILD_TRY
     cudaFree(g_keys);
     cudaFree(g_cnt);
     cudaFree(counters);
     cudaFree(d_off);
-    cudaFree(d_lut);
     if (rc != CST_OK) {
         if (t) cst_df_destroy(t);
         return rc;

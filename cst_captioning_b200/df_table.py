@@ -48,14 +48,13 @@ def unpack_keys(keys):
     return out
 
 
-def idf_values(df, n_documents):
-    """``log(n_documents) - log(max(1, df))`` with the scalar numpy calls the
-    scorer's ``counts2vec`` makes, so every value is bit-identical to it."""
+def idf_lut(n_documents):
+    """``lut[d] = log(n_documents) - log(max(1, d))`` for d = 0..n_documents with the
+    scalar numpy calls the scorer's ``counts2vec`` makes, so every value is
+    bit-identical to it (``lut[0]`` is the idf of an unseen n-gram)."""
     ref_len = np.log(float(n_documents))
-    df = np.asarray(df, dtype=np.float64)
-    uniq, inv = np.unique(df, return_inverse=True)
-    per = np.array([ref_len - np.log(max(1.0, float(u))) for u in uniq], dtype=np.float64)
-    return per[inv] if len(df) else per, float(ref_len)
+    return np.array([ref_len - np.log(max(1.0, float(d))) for d in range(int(n_documents) + 1)],
+                    dtype=np.float64)
 
 
 def _device_index(device):
@@ -82,11 +81,10 @@ class DfTable:
             raise ValueError('keys and df differ in length')
         if len(df) and df.max() > n_documents:
             raise ValueError('document frequency above the document count')
-        idf, ref_len = idf_values(df, n_documents)
-        idf = np.ascontiguousarray(idf, dtype=np.float64)
+        lut = idf_lut(n_documents)
         h = C.c_void_p()
-        check(lib.cst_df_create(keys.ctypes.data, df.ctypes.data, idf.ctypes.data, len(keys),
-                                ref_len, _device_index(device), C.byref(h)))
+        check(lib.cst_df_create(keys.ctypes.data, df.ctypes.data, len(keys), lut.ctypes.data,
+                                int(n_documents), _device_index(device), C.byref(h)))
         return cls(h, n_documents)
 
     @classmethod
@@ -124,8 +122,7 @@ class DfTable:
         dtype = _row_dtype(rows)
         off = np.ascontiguousarray(video_offsets, dtype=np.int64)
         n_videos = len(off) - 1
-        lut, _ = idf_values(np.arange(n_videos + 1, dtype=np.float64), n_videos)
-        lut = np.ascontiguousarray(lut)
+        lut = idf_lut(n_videos)
         h = C.c_void_p()
         check(lib.cst_df_build_from_rows(rows.data_ptr(), dtype, rows.shape[0], rows.shape[1],
                                          rows.stride(0), off.ctypes.data, n_videos, int(use_eos),

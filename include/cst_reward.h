@@ -71,21 +71,27 @@ const char* cst_last_error(void);
 /* ABI version of the loaded library. */
 int cst_abi_version(void);
 
+/* Number of CUDA kernels this library has launched in this process so far
+ * (instrumentation for bench.py's gpu_launches; no counterpart in the reference). */
+int64_t cst_kernel_launches(void);
+
 /* ---- document-frequency table ------------------------------------------------
  * Replaces the unpickled {'document_frequency': {ngram: df}, 'ref_len': n} dict
  * that CiderD(df=path) holds (construction site train.py:121; pickle schema
  * compute_ciderdf.py:123-129) with a device-resident open-addressing table
  * keyed by packed n-grams.
  *
- * keys[n], df[n], idf[n] are [host].  idf[i] must be
- *     log(n_documents) - log(max(1, df[i]))
- * evaluated by the caller in float64 exactly as the scorer does (the Python
- * wrapper uses numpy, so the values are bit-identical to the reference's);
- * idf_unseen is the same expression for df = 0, i.e. log(n_documents).
- * All idf must be >= 0 (df <= n_documents, which compute_ciderdf guarantees).
+ * keys[n], df[n] are [host]; df values are the integer-valued floats of the
+ * pickle.  idf_by_df [host] has n_documents + 1 entries,
+ *     idf_by_df[d] = log(n_documents) - log(max(1, d)),
+ * evaluated by the caller in float64 exactly as the scorer's counts2vec does (the
+ * Python wrapper uses numpy, so the values are bit-identical to the reference's);
+ * entry 0 is the idf of an n-gram the table does not hold.  All entries must be
+ * >= 0 (df <= n_documents, which compute_ciderdf guarantees).
  * Synchronous (one-off, like the pickle load it replaces). */
-int cst_df_create(const uint64_t* keys, const double* df, const double* idf,
-                  int64_t n, double idf_unseen, int device, cst_df_table** out);
+int cst_df_create(const uint64_t* keys, const double* df, int64_t n,
+                  const double* idf_by_df, int64_t n_documents, int device,
+                  cst_df_table** out);
 
 /* Build the table on the device from token rows: the device-side form of
  * compute_ciderdf.py:56-93 (compute_doc_freq over per-video ref sets) and of the

@@ -54,14 +54,13 @@ def test_pack_unpack_roundtrip(cst):
         cst.pack_ngrams([('1', '2', '3', '4', '5')])
 
 
-def test_idf_values_match_scorer_formula(cst):
-    from cst_captioning_b200.df_table import idf_values
-    df = np.array([1.0, 2.0, 60.0, 7.0, 2.0, 0.0])
-    idf, ref_len = idf_values(df, 60)
-    for d, w in zip(df, idf):
-        assert w == np.log(float(60)) - np.log(max(1.0, d))     # bit-identical
-    assert ref_len == np.log(60.0)
-    assert idf[2] == 0.0
+def test_idf_lut_matches_scorer_formula(cst):
+    from cst_captioning_b200.df_table import idf_lut
+    lut = idf_lut(60)
+    assert len(lut) == 61
+    for d in range(61):
+        assert lut[d] == np.log(float(60)) - np.log(max(1.0, float(d)))     # bit-identical
+    assert lut[60] == 0.0 and lut[0] == np.log(60.0)
 
 
 def test_no_silent_cpu_fallback(cst):
@@ -77,7 +76,7 @@ def test_no_silent_cpu_fallback(cst):
 def test_argument_validation_in_c(cst):
     lib = cst.lib
     out = C.c_void_p()
-    rc = lib.cst_df_create(None, None, None, 3, 1.0, 0, C.byref(out))
+    rc = lib.cst_df_create(None, None, 3, None, 5, 0, C.byref(out))
     assert rc == -1 and b'NULL' in lib.cst_last_error()
     rc = lib.cst_scb_apply(None, None, 4, 20, 9, 5, None, None, None, 0, 0, None)
     assert rc == -1 and b'unknown baseline mode' in lib.cst_last_error()
