@@ -18,6 +18,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -1130,4 +1131,66 @@ done:
     }
     *out = t;
     return CST_OK;
+}
+
+// ---------------------------------------------------------------------------
+// cst_reward_noalloc: the reward launch for hosts that cannot allocate
+// ---------------------------------------------------------------------------
+// Some hosts give every byte of HBM to their own memory pool when they start, so a
+// later cudaMalloc from a plugin simply fails; others ban allocation inside their
+// step loop because cudaMalloc / cudaFree stall the whole device.  For them the
+// statistics scratch that cst_reward takes from the caller lives here instead, in a
+// fixed array that is part of the library image.  Every GPU that loads the library
+// holds these CST_NOALLOC_SCRATCH_BYTES (about 256 KiB) until the process exits.
+#define CST_NOALLOC_SCRATCH_BYTES (256 + 16 * CST_NOALLOC_MAX_GROUPS)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[CST_NOALLOC_SCRATCH_BYTES];
+
+static std::mutex g_noalloc_mutex;
+static void* g_noalloc_ptr[64] = {nullptr};
+
+// Device address of g_noalloc_scratch on `device` (which must be current).  In host
+// code the symbol itself is only a stand-in, so the address is asked for once per
+// device and remembered.
+static int noalloc_scratch(int device, void** out) {
+    if (device < 0 || device >= 64) return fail(CST_E_RANGE, "cst_reward_noalloc: device %d outside [0, 63]", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr)
+            return fail(CST_E_CUDA, "cst_reward_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        g_noalloc_ptr[device] = ptr;
+    }
+    *out = g_noalloc_ptr[device];
+    return CST_OK;
+}
+
+extern "C" int cst_reward_noalloc(const cst_df_table* table, const void* cand, const void* greedy,
+                                  int32_t cand_dtype, int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                                  const void* refs, int32_t ref_dtype, int32_t ref_width, int64_t ref_stride,
+                                  const int64_t* ref_offsets, int32_t refs_per_video, int64_t n_videos,
+                                  int32_t cands_per_video, int32_t use_eos, int32_t mode, int32_t seq_per_img,
+                                  int32_t scb_k, const double* bcmrscores, float* reward_out, double* scores_out,
+                                  double* stats_out, void* stream) {
+    if (!table) return fail(CST_E_ARG, "cst_reward_noalloc: table is NULL");
+    if (seq_per_img < 1) return fail(CST_E_ARG, "cst_reward_noalloc: seq_per_img < 1");
+    const int64_t groups = (n_videos > n_cand / seq_per_img) ? n_videos : n_cand / seq_per_img;
+    if (groups > CST_NOALLOC_MAX_GROUPS)
+        return fail(CST_E_RANGE,
+                    "cst_reward_noalloc: %lld videos exceed the built-in scratch (CST_NOALLOC_MAX_GROUPS = %d); "
+                    "split the batch or use cst_reward with caller-provided scratch",
+                    (long long)groups, CST_NOALLOC_MAX_GROUPS);
+    void* scratch = nullptr;
+    {
+        DeviceGuard guard(table->device);
+        if (!guard.ok) return fail(CST_E_CUDA, "cst_reward_noalloc: cannot select device %d", table->device);
+        int rc = noalloc_scratch(table->device, &scratch);
+        if (rc != CST_OK) return rc;
+        // the array keeps whatever the previous call (possibly an aborted one) left:
+        // the arrival and bad-row counters must start at zero
+        CUDA_TRY(cudaMemsetAsync(scratch, 0, 256, (cudaStream_t)stream));
+    }
+    return cst_reward(table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype, ref_width,
+                      ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, mode, seq_per_img,
+                      scb_k, bcmrscores, reward_out, scores_out, stats_out, scratch, CST_NOALLOC_SCRATCH_BYTES, stream);
 }

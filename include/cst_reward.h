@@ -203,6 +203,35 @@ int cst_reward(const cst_df_table* table,
                float* reward_out, double* scores_out, double* stats_out,
                void* scratch, int64_t scratch_bytes, void* stream);
 
+/* The same launch as cst_reward for hosts that cannot allocate device memory at the
+ * time of the call: hosts that gave all of HBM to their own pool at start-up (so a
+ * plugin's cudaMalloc fails), or whose step loop bans allocation because cudaMalloc
+ * and cudaFree stall the whole device.  The statistics scratch is a fixed array
+ * inside the library instead of a caller buffer; inputs and outputs are still the
+ * caller's.  It has no counterpart in the reference.
+ *   - Limit: max(n_videos, n_cand / seq_per_img) <= CST_NOALLOC_MAX_GROUPS; larger
+ *     batches are refused with CST_E_RANGE (split them, or use cst_reward).
+ *   - Cost: about 256 KiB of device memory on every GPU that loads the library,
+ *     held until the process exits.
+ *   - The first call on a device looks the array's address up (one-time set-up);
+ *     make that first call before any stream capture begins.
+ *   - All calls on a device share the one array: two calls whose kernels overlap on
+ *     the GPU (different streams) race on it.  Serialise them.
+ *   - It calls no cudaMalloc / cudaFree or other allocating routine; its counters are
+ *     cleared on the caller's stream at the start of every call. */
+#define CST_NOALLOC_MAX_GROUPS 16384
+int cst_reward_noalloc(const cst_df_table* table,
+                       const void* cand, const void* greedy, int32_t cand_dtype,
+                       int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                       const void* refs, int32_t ref_dtype, int32_t ref_width,
+                       int64_t ref_stride, const int64_t* ref_offsets,
+                       int32_t refs_per_video, int64_t n_videos,
+                       int32_t cands_per_video, int32_t use_eos,
+                       int32_t mode, int32_t seq_per_img, int32_t scb_k,
+                       const double* bcmrscores,
+                       float* reward_out, double* scores_out, double* stats_out,
+                       void* stream);
+
 /* Baseline alone on given scores: utils.py:286-288 (WXE: scores are the
  * precomputed consensus scores) and utils.py:292-322.  scores [dev] float64
  * (n_rows, seq_per_img); for CST_BASE_GREEDY `other` holds the greedy scores, for
