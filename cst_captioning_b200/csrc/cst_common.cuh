@@ -99,39 +99,75 @@ __device__ __forceinline__ void df_probe4(const DfView& t, const u64 key[4], con
 __device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u; }
 
 // ---------------------------------------------------------------------------
-// Row canonicalisation + n-gram keys, one warp per row, lane = token position.
+// Row canonicalisation + n-gram keys.  A row is handled by a group of G lanes:
+// G = 32 (one row per warp) or G = 16 (two rows per warp, one per half -- captions
+// average 11 tokens, so half-warps double the useful lanes; rows whose canonical
+// length exceeds 16 are redone with G = 32 by the caller).  `sl` = lane within the
+// group = n-gram start position, `sub` = which half.
 // Restates utils.py:135-152 (array_to_str) and compute_ciderdf.py:28-33
 // (precook's k/i loops) on packed keys.
-//   key[k]   packed (k+1)-gram starting at this lane's position, 0 if none
-//   L        canonical token count (warp uniform)
+//   key[k]   packed (k+1)-gram starting at position sl, 0 if none
+//   L        canonical token count of the group's row
 //   returns  true if the row held an id outside [-1, 65534] before its end
-// tokbuf: 32 u32 of warp-private shared memory.
+// tokbuf: 32 u32 of warp-private shared memory (G = 16: 16 per half).
 // ---------------------------------------------------------------------------
+template <int G>
+struct Grp {
+    static_assert(G == 16 || G == 32, "row group is a warp or a half-warp");
+    __device__ static __forceinline__ int sub(int lane) { return G == 32 ? 0 : (lane >> 4); }
+    __device__ static __forceinline__ int sl(int lane) { return G == 32 ? lane : (lane & 15); }
+    __device__ static __forceinline__ u32 mask(int lane) { return G == 32 ? CST_FULL : (0xffffu << (lane & 16)); }
+    // 32-bit mask over the row's (up to 32) raw positions: pa speaks for position sl,
+    // pb for position sl + 16 (G = 16 only; each lane holds two raw tokens there).
+    __device__ static __forceinline__ u32 vote(bool pa, bool pb, int lane) {
+        const u32 a = __ballot_sync(CST_FULL, pa);
+        if (G == 32) return a;
+        const u32 b = __ballot_sync(CST_FULL, pb);
+        const int sh = lane & 16;
+        return ((a >> sh) & 0xffffu) | (((b >> sh) & 0xffffu) << 16);
+    }
+};
+
 template <typename T>
-__device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, int use_eos,
-                                          int lane, u32* tokbuf, u64 key[4], int& L) {
-    const bool in = lane < width;
-    long long t = in ? (long long)__ldcs(row + lane) : 0ll;   // rows stream through once: evict-first
-    const bool bad = in && (t < -1 || t > 65534);
-    const bool term = in && (t == 0 || t == -1 || bad);   // -1 = padding: ends the row, never emitted
-    const u32 tmask = __ballot_sync(CST_FULL, term);
-    const u32 bmask = __ballot_sync(CST_FULL, bad);
-    const int end = tmask ? (__ffs(tmask) - 1) : width;   // first <end> (or bad id), else row width
+__device__ __forceinline__ long long ld_tok(const T* p) {
+    return (long long)__ldcs(p);          // rows stream through once: evict-first
+}
+
+template <typename T, int G>
+__device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, int use_eos, int lane,
+                                          u32* tokbuf, u64 key[4], int& L) {
+    typedef Grp<G> Gp;
+    const int sl = Gp::sl(lane);
+    const int pa = sl, pb = sl + 16;                       // raw positions this lane owns
+    const bool ina = pa < width;
+    const bool inb = (G == 16) && pb < width;
+    const long long ta = ina ? ld_tok(row + pa) : 0ll;
+    const long long tb = inb ? ld_tok(row + pb) : 0ll;
+    const bool bada = ina && (ta < -1 || ta > 65534);
+    const bool badb = inb && (tb < -1 || tb > 65534);
+    // -1 = padding: ends the row, never emitted
+    const u32 tmask = Gp::vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane);
+    const u32 bmask = Gp::vote(bada, badb, lane);
+    const int end = tmask ? (__ffs(tmask) - 1) : width;    // first <end> (or bad id), else row width
     const u32 upto_end = (end >= 31) ? CST_FULL : ((2u << end) - 1u);
-    const bool keep = (lane < end && t != 1) || (use_eos && lane == end && in && t == 0);
-    const u32 kmask = __ballot_sync(CST_FULL, keep);
+    const bool keepa = (pa < end && ta != 1) || (use_eos && pa == end && ina && ta == 0);
+    const bool keepb = (G == 16) && ((pb < end && tb != 1) || (use_eos && pb == end && inb && tb == 0));
+    const u32 kmask = Gp::vote(keepa, keepb, lane);
     L = __popc(kmask);
-    const int pos = __popc(kmask & lanemask_lt(lane));
-    if (keep) tokbuf[pos] = (u32)t + 1u;
+    u32* buf = tokbuf + Gp::sub(lane) * 16;
+    if (G == 32 || L <= 16) {                              // G = 16: longer rows are redone by the caller
+        if (keepa) buf[__popc(kmask & lanemask_lt(pa))] = (u32)ta + 1u;
+        if (keepb) buf[__popc(kmask & lanemask_lt(pb))] = (u32)tb + 1u;
+    }
     __syncwarp();
-    const u32 e0 = (lane < L) ? tokbuf[lane] : 0u;
+    const u32 e0 = (sl < L && (G == 32 || L <= 16)) ? buf[sl] : 0u;
     __syncwarp();
-    u32 e1 = __shfl_down_sync(CST_FULL, e0, 1);
-    u32 e2 = __shfl_down_sync(CST_FULL, e0, 2);
-    u32 e3 = __shfl_down_sync(CST_FULL, e0, 3);
-    if (lane + 1 >= L) e1 = 0;
-    if (lane + 2 >= L) e2 = 0;
-    if (lane + 3 >= L) e3 = 0;
+    u32 e1 = __shfl_down_sync(CST_FULL, e0, 1, G);
+    u32 e2 = __shfl_down_sync(CST_FULL, e0, 2, G);
+    u32 e3 = __shfl_down_sync(CST_FULL, e0, 3, G);
+    if (sl + 1 >= L || sl + 1 >= G) e1 = 0;
+    if (sl + 2 >= L || sl + 2 >= G) e2 = 0;
+    if (sl + 3 >= L || sl + 3 >= G) e3 = 0;
     const u64 k1 = (u64)e0;
     const u64 k2 = k1 | ((u64)e1 << 16);
     const u64 k3 = k2 | ((u64)e2 << 32);
@@ -143,41 +179,54 @@ __device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, 
     return (bmask & upto_end) != 0u;
 }
 
-// Term frequency of each lane's n-gram inside its own row via MATCH.ANY; the
-// lowest lane of every group of equal keys is the group's leader (the dict entry
-// precook would create at that position).
+// Term frequency of each lane's n-gram inside its own row via MATCH.ANY (restricted
+// to the row's lane group); the lowest lane of every set of equal keys is the leader
+// (the dict entry precook would create at that position).
+template <int G>
 __device__ __forceinline__ void row_tf(const u64 key[4], int lane, int tf[4], bool lead[4]) {
+    const u32 gm = Grp<G>::mask(lane);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        const u32 m = __match_any_sync(CST_FULL, key[k]);
+        const u32 m = __match_any_sync(CST_FULL, key[k]) & gm;
         tf[k] = __popc(m);
         lead[k] = (key[k] != 0ull) && ((__ffs(m) - 1) == lane);
     }
 }
 
-// Sum four per-lane doubles over the warp with a transposed butterfly: 6 exchanges
-// instead of 20.  On return every lane holds the warp total of ONE of the four
-// inputs: order o = 2 * bit4(lane) + bit3(lane).
-__device__ __forceinline__ double warp_sum4_transposed(const double v[4], int lane) {
-    const bool hi16 = (lane & 16) != 0;
-    const bool hi8 = (lane & 8) != 0;
-    // exchange with lane^16: low half keeps orders {0,1}, high half keeps {2,3}
-    double sendA = hi16 ? v[0] : v[2];
-    double sendB = hi16 ? v[1] : v[3];
-    double keepA = hi16 ? v[2] : v[0];
-    double keepB = hi16 ? v[3] : v[1];
-    keepA += __shfl_xor_sync(CST_FULL, sendA, 16);
-    keepB += __shfl_xor_sync(CST_FULL, sendB, 16);
-    // exchange with lane^8: bit3 == 0 keeps the first of the pair, bit3 == 1 the second
-    double send = hi8 ? keepA : keepB;
-    double x = hi8 ? keepB : keepA;
-    x += __shfl_xor_sync(CST_FULL, send, 8);
-    x += __shfl_xor_sync(CST_FULL, x, 4);
-    x += __shfl_xor_sync(CST_FULL, x, 2);
-    x += __shfl_xor_sync(CST_FULL, x, 1);
+// Sum four per-lane doubles over a lane group with a transposed butterfly (G = 32:
+// 6 exchanges instead of 20).  On return every lane holds the group total of ONE of
+// the four inputs: order o = group_order<G>(lane).
+template <int G>
+__device__ __forceinline__ double group_sum4_transposed(const double v[4], int lane) {
+    constexpr int HI = G / 2, MID = G / 4;
+    const bool hi = (lane & HI) != 0;
+    const bool mid = (lane & MID) != 0;
+    // exchange with lane^HI: low half keeps orders {0,1}, high half keeps {2,3}
+    const double sendA = hi ? v[0] : v[2];
+    const double sendB = hi ? v[1] : v[3];
+    double keepA = hi ? v[2] : v[0];
+    double keepB = hi ? v[3] : v[1];
+    keepA += __shfl_xor_sync(CST_FULL, sendA, HI);
+    keepB += __shfl_xor_sync(CST_FULL, sendB, HI);
+    // exchange with lane^MID: bit clear keeps the first of the pair, bit set the second
+    const double send = mid ? keepA : keepB;
+    double x = mid ? keepB : keepA;
+    x += __shfl_xor_sync(CST_FULL, send, MID);
+#pragma unroll
+    for (int o = MID / 2; o > 0; o >>= 1) x += __shfl_xor_sync(CST_FULL, x, o);
     return x;
 }
-__device__ __forceinline__ int lane_order(int lane) { return ((lane >> 4) & 1) * 2 + ((lane >> 3) & 1); }
+template <int G>
+__device__ __forceinline__ int group_order(int lane) {
+    return ((lane & (G / 2)) ? 2 : 0) + ((lane & (G / 4)) ? 1 : 0);
+}
+// sum of the four per-order values held by group_sum4_transposed's layout
+template <int G>
+__device__ __forceinline__ double group_sum_orders(double t) {
+    t += __shfl_xor_sync(CST_FULL, t, G / 2);
+    t += __shfl_xor_sync(CST_FULL, t, G / 4);
+    return t;
+}
 
 __device__ __forceinline__ double inv_norm_of(double sumsq) {
     return sumsq > 0.0 ? rsqrt(sumsq) : 0.0;
@@ -201,7 +250,11 @@ __device__ __forceinline__ u64 count_key(u32 slot, u32 r) {
     return (1ull << 63) | ((u64)slot << 24) | ((u64)r << 16);
 }
 
-__device__ __forceinline__ u32 vid_insert(VidSlot* tab, u32 mask, u32 idx, u64 key) {
+// The table capacity is any number (sized to the worst case of the staged refs, not
+// rounded to a power of two: shared memory decides how many CTAs fit an SM).
+__device__ __forceinline__ u32 vid_home(u32 h, u32 slots) { return __umulhi(h, slots); }
+
+__device__ __forceinline__ u32 vid_insert(VidSlot* tab, u32 slots, u32 idx, u64 key) {
     for (;;) {
         u64 cur = *reinterpret_cast<volatile u64*>(&tab[idx].key);
         if (cur == key) return idx;
@@ -209,16 +262,16 @@ __device__ __forceinline__ u32 vid_insert(VidSlot* tab, u32 mask, u32 idx, u64 k
             u64 old = atomicCAS(reinterpret_cast<u64*>(&tab[idx].key), 0ull, key);
             if (old == 0ull || old == key) return idx;
         }
-        idx = (idx + 1) & mask;
+        idx = (idx + 1 == slots) ? 0u : idx + 1;
     }
 }
 
-__device__ __forceinline__ int vid_find(const VidSlot* tab, u32 mask, u32 idx, u64 key) {
+__device__ __forceinline__ int vid_find(const VidSlot* tab, u32 slots, u32 idx, u64 key) {
     for (;;) {
         u64 cur = tab[idx].key;
         if (cur == key) return (int)idx;
         if (cur == 0ull) return -1;
-        idx = (idx + 1) & mask;
+        idx = (idx + 1 == slots) ? 0u : idx + 1;
     }
 }
 

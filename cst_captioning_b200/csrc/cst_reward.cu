@@ -322,10 +322,10 @@ __global__ void k_ngram_counts(const T* __restrict__ rows, int64_t n_rows, int w
     if (row >= n_rows) return;
     u64 key[4];
     int L;
-    canon_row<T>(rows + row * stride, width, use_eos, lane, tokbuf[warp], key, L);
+    canon_row<T, 32>(rows + row * stride, width, use_eos, lane, tokbuf[warp], key, L);
     int tf[4];
     bool lead[4];
-    row_tf(key, lane, tf, lead);
+    row_tf<32>(key, lane, tf, lead);
     int base = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -500,39 +500,41 @@ struct ScoreParams {
     u32* ctl;
     double* partials;
     double n_m, n_b;
-    u32 tab_slots;        // power of two
-    int tab_shift;        // 32 - log2(tab_slots)
+    u32 tab_slots;        // capacity of the per-video shared table
 };
 
-#define CST_MAX_WARPS 20
+#define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
 
-// Phase R for one reference row (one warp).
-template <typename RT>
-__device__ __forceinline__ bool ref_phase(const ScoreParams& p, const RT* row, int rl, int lane, VidSlot* tab,
-                                          double* invn, int* lenr, u32* tokbuf) {
+// Phase R for one reference row per lane group (G = 32: one row, G = 16: two rows of
+// this warp, one per half).  `width` = 0 marks an idle group (odd row count).
+// Returns the canonical length (so the caller can redo rows longer than G) and
+// whether the row held a bad id.
+template <typename RT, int G>
+__device__ __forceinline__ int ref_phase(const ScoreParams& p, const RT* row, int width, int rl, int lane,
+                                         VidSlot* tab, double* invn, int* lenr, u32* tokbuf, bool& bad) {
     u64 key[4];
     int L;
-    const bool bad = canon_row<RT>(row, p.ref_width, p.use_eos, lane, tokbuf, key, L);
+    bad = canon_row<RT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
+    if (G == 16 && __any_sync(CST_FULL, L > 16)) return L;      // warp-uniform: redo both rows with G = 32
     int tf[4];
     bool lead[4];
-    row_tf(key, lane, tf, lead);
+    row_tf<G>(key, lane, tf, lead);
     u32 h[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
     double idf[4];
     df_probe4(p.df, key, h, lead, idf);
 
-    const u32 mask = p.tab_slots - 1u;
     const u32 bit = 1u << rl;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         if (lead[k]) {
-            const u32 idx = vid_insert(tab, mask, h[k] >> p.tab_shift, key[k]);
+            const u32 idx = vid_insert(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
             atomicOr(&tab[idx].P, bit);
             if (tf[k] > 1) {
                 atomicOr(&tab[idx].M, bit);
                 const u64 ck = count_key(idx, (u32)rl);
-                const u32 j = vid_insert(tab, mask, cst_hash(ck) >> p.tab_shift, ck);
+                const u32 j = vid_insert(tab, p.tab_slots, vid_home(cst_hash(ck), p.tab_slots), ck);
                 tab[j].P = (u32)tf[k];
             }
         }
@@ -543,33 +545,38 @@ __device__ __forceinline__ bool ref_phase(const ScoreParams& p, const RT* row, i
         const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
         n2[k] = w * w;                                             // norm += vec ** 2
     }
-    const double tot = warp_sum4_transposed(n2, lane);
-    if ((lane & 7) == 0) invn[lane_order(lane) * 32 + rl] = inv_norm_of(tot);
-    if (lane == 0) lenr[rl] = (L > 1) ? (L - 1) : 0;               // "length" = bigram count
-    return bad;
+    const double tot = group_sum4_transposed<G>(n2, lane);
+    if (width > 0) {
+        if ((lane & (G / 4 - 1)) == 0) invn[group_order<G>(lane) * 32 + rl] = inv_norm_of(tot);
+        if (Grp<G>::sl(lane) == 0) lenr[rl] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
+    }
+    return L;
 }
 
-// Phase C for one candidate row (one warp): sum over the chunk's refs of
-// sum_n sim_n / (norm_h[n] norm_r[n]) * penalty  (not yet / n, / R, * 10).
-template <typename CT>
-__device__ __forceinline__ double cand_phase(const ScoreParams& p, const CT* row, int nref, int lane,
-                                             const VidSlot* tab, const double* invn, const int* lenr,
-                                             double* gh, u32* tokbuf, bool& bad) {
+// Phase C for one candidate row per lane group: sum over the chunk's refs of
+// sum_n sim_n / (norm_h[n] norm_r[n]) * penalty  (not yet / n, / R, * 10), returned
+// in `score` on every lane of the group.
+template <typename CT, int G>
+__device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, int width, int nref, int lane,
+                                          const VidSlot* tab, const double* invn, const int* lenr, double* gh,
+                                          u32* tokbuf, bool& bad, double& score) {
     u64 key[4];
     int L;
-    bad = canon_row<CT>(row, p.cand_width, p.use_eos, lane, tokbuf, key, L);
+    bad = canon_row<CT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
+    if (G == 16 && __any_sync(CST_FULL, L > 16)) return L;
     int tf[4];
     bool lead[4];
-    row_tf(key, lane, tf, lead);
+    row_tf<G>(key, lane, tf, lead);
     u32 h[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
     double idf[4];
     df_probe4(p.df, key, h, lead, idf);
 
-    // Gaussian length penalty against every ref of the chunk
+    // Gaussian length penalty against every ref of the chunk (per-group buffer)
     const int lenh = (L > 1) ? (L - 1) : 0;
-    if (lane < nref) gh[lane] = __ldg(p.gauss + (lenh - lenr[lane] + CST_GAUSS_HALF));
+    double* g = gh + Grp<G>::sub(lane) * 32;
+    for (int r = Grp<G>::sl(lane); r < nref; r += G) g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
     __syncwarp();
 
     double n2[4];
@@ -578,61 +585,60 @@ __device__ __forceinline__ double cand_phase(const ScoreParams& p, const CT* row
         const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;
         n2[k] = w * w;
     }
-    const double invh = inv_norm_of(warp_sum4_transposed(n2, lane));
+    const double invh = inv_norm_of(group_sum4_transposed<G>(n2, lane));
 
-    const u32 mask = p.tab_slots - 1u;
     double num[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         double inner = 0.0;
         if (lead[k]) {
-            const int idx = vid_find(tab, mask, h[k] >> p.tab_shift, key[k]);
+            const int idx = vid_find(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
             if (idx >= 0) {
-                u32 P = tab[idx].P;
                 const u32 M = tab[idx].M;
+                u32 P = tab[idx].P & ~M;
                 const double* inv_k = invn + k * 32;
-                while (P) {
+                while (P) {                               // refs holding the n-gram once: min(tf_h, 1) * 1
                     const int r = __ffs(P) - 1;
                     P &= P - 1u;
-                    const double cf = inv_k[r] * gh[r];
-                    if (!((M >> r) & 1u)) {
-                        inner += cf;                     // ref count 1: min(tf_h, 1) * 1
-                    } else {
-                        const u64 ck = count_key((u32)idx, (u32)r);
-                        const int j = vid_find(tab, mask, cst_hash(ck) >> p.tab_shift, ck);
-                        const int c = (int)tab[j].P;
-                        const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
-                        inner += (double)m * cf;
-                    }
+                    inner += inv_k[r] * g[r];
+                }
+                u32 Q = M;
+                while (Q) {                               // refs holding it more than once: exact count
+                    const int r = __ffs(Q) - 1;
+                    Q &= Q - 1u;
+                    const u64 ck = count_key((u32)idx, (u32)r);
+                    const int j = vid_find(tab, p.tab_slots, vid_home(cst_hash(ck), p.tab_slots), ck);
+                    const int c = (int)tab[j].P;
+                    const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
+                    inner += (double)m * (inv_k[r] * g[r]);
                 }
             }
         }
         num[k] = idf[k] * idf[k] * inner;
     }
-    double t = warp_sum4_transposed(num, lane) * invh;
-    t += __shfl_xor_sync(CST_FULL, t, 16);
-    t += __shfl_xor_sync(CST_FULL, t, 8);
+    score = group_sum_orders<G>(group_sum4_transposed<G>(num, lane) * invh);
     __syncwarp();
-    return t;
+    return L;
 }
 
 template <typename CT, typename RT>
-__global__ void __launch_bounds__(CST_MAX_WARPS * 32, 2) k_score(const ScoreParams p) {
+__global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
+    const int sub = lane >> 4;
     const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
 
     VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
     double* invn = reinterpret_cast<double*>(tab + p.tab_slots);   // [4][32]
-    double* gh_all = invn + 128;                                    // [nwarps][32]
-    double* sc = gh_all + nwarps * 32;                              // [n_local]
+    double* gh_all = invn + 128;                                    // [nwarps][2][32]
+    double* sc = gh_all + nwarps * 64;                              // [n_local]
     double* sorted = sc + n_local;                                  // [cands_per_video]
     double* red = sorted + p.cands_per_video;                       // [2 * nwarps]
     int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
     u32* tok_all = reinterpret_cast<u32*>(lenr + 32);               // [nwarps][32]
-    double* gh = gh_all + warp * 32;
+    double* gh = gh_all + warp * 64;
     u32* tokbuf = tok_all + warp * 32;
 
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
@@ -655,19 +661,50 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 2) k_score(const ScorePara
                 for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
             }
             __syncthreads();
-            for (int rl = warp; rl < nref; rl += nwarps) {
-                const RT* row = reinterpret_cast<const RT*>(p.refs) + (c0 + rl) * p.ref_stride;
-                if (ref_phase<RT>(p, row, rl, lane, tab, invn, lenr, tokbuf)) bad_rows += (lane == 0);
+            // ---- phase R: two reference rows per warp ----
+            for (int base = 2 * warp; base < nref; base += 2 * nwarps) {
+                const RT* rows = reinterpret_cast<const RT*>(p.refs) + (c0 + base) * p.ref_stride;
+                const int rl = base + sub;
+                const bool act = rl < nref;
+                bool bad;
+                const int L = ref_phase<RT, 16>(p, rows + (act ? sub : 0) * p.ref_stride, act ? p.ref_width : 0, rl,
+                                                lane, tab, invn, lenr, tokbuf, bad);
+                if (__any_sync(CST_FULL, L > 16)) {          // a long row: redo the pair one row per warp
+                    for (int q = 0; q < 2 && base + q < nref; ++q) {
+                        ref_phase<RT, 32>(p, rows + q * p.ref_stride, p.ref_width, base + q, lane, tab, invn, lenr,
+                                          tokbuf, bad);
+                        if (bad && lane == 0) ++bad_rows;
+                    }
+                } else if (bad && act && (lane & 15) == 0) {
+                    ++bad_rows;
+                }
             }
             __syncthreads();
-            for (int c = warp; c < n_local; c += nwarps) {
-                const bool is_greedy = c >= p.cands_per_video;
-                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
-                const CT* base = reinterpret_cast<const CT*>(is_greedy ? p.greedy : p.cand);
+            // ---- phase C: two candidate rows per warp ----
+            for (int base = 2 * warp; base < n_local; base += 2 * nwarps) {
+                const int c = base + sub;
+                const bool act = c < n_local;
+                const int cc = act ? c : base;
+                const bool is_greedy = cc >= p.cands_per_video;
+                const int64_t ci = video * p.cands_per_video + (is_greedy ? cc - p.cands_per_video : cc);
+                const CT* row = reinterpret_cast<const CT*>(is_greedy ? p.greedy : p.cand) + ci * p.cand_stride;
                 bool bad;
-                const double t = cand_phase<CT>(p, base + ci * p.cand_stride, nref, lane, tab, invn, lenr, gh,
-                                                tokbuf, bad);
-                if (lane == 0) {
+                double t = 0.0;
+                const int L = cand_phase<CT, 16>(p, row, act ? p.cand_width : 0, nref, lane, tab, invn, lenr, gh,
+                                                 tokbuf, bad, t);
+                if (__any_sync(CST_FULL, L > 16)) {
+                    for (int q = 0; q < 2 && base + q < n_local; ++q) {
+                        const int cq = base + q;
+                        const bool gq = cq >= p.cands_per_video;
+                        const int64_t cqi = video * p.cands_per_video + (gq ? cq - p.cands_per_video : cq);
+                        const CT* rq = reinterpret_cast<const CT*>(gq ? p.greedy : p.cand) + cqi * p.cand_stride;
+                        cand_phase<CT, 32>(p, rq, p.cand_width, nref, lane, tab, invn, lenr, gh, tokbuf, bad, t);
+                        if (lane == 0) {
+                            sc[cq] += t;
+                            if (bad && c0 == r0) ++bad_rows;
+                        }
+                    }
+                } else if (act && (lane & 15) == 0) {
                     sc[c] += t;
                     if (bad && c0 == r0) ++bad_rows;
                 }
@@ -839,16 +876,15 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     // every n-gram instance of the staged refs gets at most one slot (plus, for an
     // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
     const u32 worst = (u32)p.chunk_refs * (u32)grams_per_row(ref_width);
-    p.tab_slots = next_pow2(worst + worst / 4 + 8);
+    p.tab_slots = worst + worst / 4 + 8;
     if (p.tab_slots < 64) p.tab_slots = 64;
-    p.tab_shift = 32 - __builtin_ctz(p.tab_slots);
 
     const int n_local = cands_per_video * (greedy ? 2 : 1);
-    int nwarps = p.chunk_refs > n_local ? p.chunk_refs : n_local;
+    int nwarps = ((p.chunk_refs > n_local ? p.chunk_refs : n_local) + 1) / 2;   // two rows per warp
     if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
     if (nwarps < 4) nwarps = 4;
     const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
-                        (size_t)nwarps * 32 * sizeof(double) + (size_t)n_local * sizeof(double) +
+                        (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
                         (size_t)cands_per_video * sizeof(double) + (size_t)2 * nwarps * sizeof(double) +
                         32 * sizeof(int) + (size_t)nwarps * 32 * sizeof(u32);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
@@ -976,11 +1012,11 @@ __global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, in
         for (int64_t r = r0 + warp; r < r1; r += nwarps) {
             u64 key[4];
             int L;
-            const bool bad = canon_row<T>(rows + r * stride, width, use_eos, lane, tokbuf, key, L);
+            const bool bad = canon_row<T, 32>(rows + r * stride, width, use_eos, lane, tokbuf, key, L);
             if (bad && lane == 0) atomicAdd(n_bad, 1u);
             int tf[4];
             bool lead[4];
-            row_tf(key, lane, tf, lead);
+            row_tf<32>(key, lane, tf, lead);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 if (!lead[k]) continue;
