@@ -371,9 +371,17 @@ extern "C" int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows,
 // ---------------------------------------------------------------------------
 // baseline (phase B): utils.py:292-322 and 219-224 on one group of S scores
 // ---------------------------------------------------------------------------
-// Sum of the k lowest of x[0..S) (ties broken by index, like a stable sort);
-// `sorted` is S doubles of scratch.  One warp.
-__device__ __forceinline__ double k_lowest_sum(const double* x, int S, int k, int lane, double* sorted) {
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(CST_FULL, v, o);
+    return v;
+}
+
+// Sum of the k lowest of x[0..S) by one warp: every lane ranks its elements by
+// counting (ties broken by index, like a stable sort) and the elements of rank < k are
+// summed with a fixed shuffle tree (deterministic).
+__device__ __forceinline__ double k_lowest_sum(const double* x, int S, int k, int lane) {
+    double acc = 0.0;
     for (int i = lane; i < S; i += 32) {
         const double xi = x[i];
         int rank = 0;
@@ -381,39 +389,26 @@ __device__ __forceinline__ double k_lowest_sum(const double* x, int S, int k, in
             const double xj = x[j];
             rank += (xj < xi || (xj == xi && j < i)) ? 1 : 0;
         }
-        sorted[rank] = xi;
+        if (rank < k) acc += xi;
     }
-    __syncwarp();
-    double s = 0.0;
-    if (lane == 0) {
-        s = sorted[0];
-        for (int i = 1; i < k; ++i) s += sorted[i];   // ascending, the order np.mean(sorted[:k]) sees
-    }
-    __syncwarp();
-    return __shfl_sync(CST_FULL, s, 0);
-}
-
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(CST_FULL, v, o);
-    return v;
+    return warp_sum(acc);
 }
 
 // One warp turns the S scores of a group into rewards and the group's partial
 // statistics.  sc: S sampled scores (shared or global); other: greedy scores
 // (GREEDY) or bcmrscores row (SCB_GT); reward: global float out.
 __device__ __forceinline__ void baseline_group(const double* sc, const double* other, int S, int mode, int k,
-                                               int lane, double* sorted, float* reward, double& sum_m,
+                                               int lane, float* reward, double& sum_m,
                                                double& sum_b) {
     double base = 0.0;
     double sb = 0.0;
     if (mode == CST_BASE_SCB_GT) {
-        base = k_lowest_sum(other, S, k, lane, sorted) / (double)k;
+        base = k_lowest_sum(other, S, k, lane) / (double)k;
         double a = 0.0;
         for (int i = lane; i < S; i += 32) a += other[i];
         sb = warp_sum(a);
     } else if (mode == CST_BASE_SCB_SAMPLE) {
-        const double low = k_lowest_sum(sc, S, k, lane, sorted);
+        const double low = k_lowest_sum(sc, S, k, lane);
         base = low / (double)k;
         sb = low;
     }
@@ -572,13 +567,6 @@ __device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, i
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
     double idf[4];
     df_probe4(p.df, key, h, lead, idf);
-
-    // Gaussian length penalty against every ref of the chunk (per-group buffer)
-    const int lenh = (L > 1) ? (L - 1) : 0;
-    double* g = gh + Grp<G>::sub(lane) * 32;
-    for (int r = Grp<G>::sl(lane); r < nref; r += G) g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
-    __syncwarp();
-
     double n2[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -586,6 +574,12 @@ __device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, i
         n2[k] = w * w;
     }
     const double invh = inv_norm_of(group_sum4_transposed<G>(n2, lane));
+
+    // Gaussian length penalty against every ref of the chunk (per-group buffer)
+    const int lenh = (L > 1) ? (L - 1) : 0;
+    double* g = gh + Grp<G>::sub(lane) * 32;
+    for (int r = Grp<G>::sl(lane); r < nref; r += G) g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
+    __syncwarp();
 
     double num[4];
 #pragma unroll
@@ -634,8 +628,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
     double* invn = reinterpret_cast<double*>(tab + p.tab_slots);   // [4][32]
     double* gh_all = invn + 128;                                    // [nwarps][2][32]
     double* sc = gh_all + nwarps * 64;                              // [n_local]
-    double* sorted = sc + n_local;                                  // [cands_per_video]
-    double* red = sorted + p.cands_per_video;                       // [2 * nwarps]
+    double* red = sc + n_local;                                     // [2 * nwarps]
     int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
     u32* tok_all = reinterpret_cast<u32*>(lenr + 32);               // [nwarps][32]
     double* gh = gh_all + warp * 64;
@@ -679,7 +672,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                     ++bad_rows;
                 }
             }
-            __syncthreads();
+            __syncthreads();                         // the video table is complete
             // ---- phase C: two candidate rows per warp ----
             for (int base = 2 * warp; base < n_local; base += 2 * nwarps) {
                 const int c = base + sub;
@@ -709,33 +702,36 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                     if (bad && c0 == r0) ++bad_rows;
                 }
             }
-            __syncthreads();
+            __syncthreads();                         // all probes done before the table is cleared again
         }
-
-        // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
-        for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
-            double s = sc[c] * 0.25;
-            s = (R > 0) ? s / (double)R : 0.0;
-            s *= 10.0;
-            sc[c] = s;
-            if (p.scores) {
-                const bool is_greedy = c >= p.cands_per_video;
-                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
-                p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
-            }
-        }
+        if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
         if (bad_rows && p.ctl) atomicAdd(&p.ctl[1], bad_rows);
-        __syncthreads();
 
-        if (p.mode >= 0 && warp == 0) {
-            const int S = p.cands_per_video;
-            const double* other = (p.mode == CST_BASE_GREEDY) ? (sc + S)
-                                  : (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : nullptr;
-            double sm, sb;
-            baseline_group(sc, other, S, p.mode, p.scb_k, lane, sorted, p.reward + video * S, sm, sb);
-            if (lane == 0) {
-                p.partials[2 * video] = sm;
-                p.partials[2 * video + 1] = sb;
+        // ---- phase B (warp 0): finish the scores, baseline, rewards, statistics ----
+        if (warp == 0) {
+            // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
+            for (int c = lane; c < n_local; c += 32) {
+                double s = sc[c] * 0.25;
+                s = (R > 0) ? s / (double)R : 0.0;
+                s *= 10.0;
+                sc[c] = s;
+                if (p.scores) {
+                    const bool is_greedy = c >= p.cands_per_video;
+                    const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
+                    p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
+                }
+            }
+            __syncwarp();
+            if (p.mode >= 0) {
+                const int S = p.cands_per_video;
+                const double* other = (p.mode == CST_BASE_GREEDY) ? (sc + S)
+                                      : (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : nullptr;
+                double sm, sb;
+                baseline_group(sc, other, S, p.mode, p.scb_k, lane, p.reward + video * S, sm, sb);
+                if (lane == 0) {
+                    p.partials[2 * video] = sm;
+                    p.partials[2 * video + 1] = sb;
+                }
             }
         }
         __syncthreads();
@@ -749,12 +745,10 @@ __global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, 
                                              double* stats, u32* ctl, double* partials, double n_m, double n_b) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* red = reinterpret_cast<double*>(smem);   // [8]
-    double* sorted_all = red + 8;                    // [4][S]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int64_t g = (int64_t)blockIdx.x * 4 + warp; g < n_groups; g += (int64_t)gridDim.x * 4) {
         double sm, sb;
-        baseline_group(scores + g * S, other ? other + g * S : nullptr, S, mode, k, lane, sorted_all + warp * S,
-                       reward + g * S, sm, sb);
+        baseline_group(scores + g * S, other ? other + g * S : nullptr, S, mode, k, lane, reward + g * S, sm, sb);
         if (lane == 0) {
             partials[2 * g] = sm;
             partials[2 * g + 1] = sb;
@@ -885,7 +879,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (nwarps < 4) nwarps = 4;
     const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
                         (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
-                        (size_t)cands_per_video * sizeof(double) + (size_t)2 * nwarps * sizeof(double) +
+                        (size_t)2 * nwarps * sizeof(double) +
                         32 * sizeof(int) + (size_t)nwarps * 32 * sizeof(u32);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 
@@ -932,10 +926,7 @@ extern "C" int cst_scb_apply(const double* scores, const double* other, int64_t 
     if (!guard.ok) return fail(CST_E_CUDA, "cst_scb_apply: cannot select device %d", device);
     double n_m, n_b;
     stat_counts(mode, n_rows * seq_per_img, seq_per_img, scb_k, n_m, n_b);
-    const size_t smem = (8 + (size_t)4 * seq_per_img) * sizeof(double);
-    if (smem > 48 * 1024) {
-        CUDA_TRY(cudaFuncSetAttribute(k_scb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    }
+    const size_t smem = 8 * sizeof(double);
     int64_t blocks = (n_rows + 3) / 4;
     if (blocks > 148 * 16) blocks = 148 * 16;
     k_scb<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
