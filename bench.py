@@ -21,6 +21,8 @@ import time
 
 import numpy as np
 
+os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')   # stdout carries the one JSON line only
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -290,13 +292,14 @@ def product_arm(args):
     out_pin = torch.empty(n_cap, dtype=torch.float32).pin_memory()
     st_pin = torch.empty(5, dtype=torch.float64).pin_memory()
 
+    pipe = cst.HostRewardPipeline(scorer, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1,
+                                  slices=args.e2e_slices)
+
     def e2e_step():
-        c = h_cand.to(dev, non_blocking=True)
-        r = h_refs.to(dev, non_blocking=True)
-        rew, m, b, st = cst.get_cst_reward(c, r, scorer, **kw)
+        # public API for host-resident batches: pinned rows in, pinned rewards + statistics out
+        _, st = pipe(h_cand, h_refs, out=out_pin)
         if world > 1:
             dist.all_reduce(st)
-        out_pin.copy_(rew[:, 0], non_blocking=True)
         st_pin.copy_(st, non_blocking=True)
         torch.cuda.synchronize()
 
@@ -314,6 +317,7 @@ def product_arm(args):
     e2e = {'value': world * n_cap * e2e_steps / e2e_s, 'unit': UNIT,
            'h2d_bytes_per_step': int(h_cand.numel() * 4 + h_refs.numel() * 4),
            'd2h_bytes_per_step': int(out_pin.numel() * 4 + st_pin.numel() * 8), 'steps': e2e_steps,
+           'api': 'HostRewardPipeline (pinned host rows, %d slices, upload overlapped with scoring)' % args.e2e_slices,
            'ms_per_step': 1e3 * e2e_s / e2e_steps}
 
     # ---- CPU baseline: oracle port, one core, bounded sample (rank 0, N = 1 only) --
@@ -351,6 +355,7 @@ def main():
     ap.add_argument('--videos', type=int, default=65536, help='videos per GPU per step')
     ap.add_argument('--cpu-videos', type=int, default=160, help='CPU-baseline sample size (videos)')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--e2e-slices', type=int, default=16, help='video slices of the host pipeline')
     args = ap.parse_args()
     if args.impl == 'reference':
         return reference_arm(args)

@@ -7,6 +7,7 @@ Public surface (mirrors the reference's interfaces for this path):
 * :func:`get_self_critical_reward`     <- ``utils.get_self_critical_reward`` (``utils.py:169``)
 * :class:`DfTable`                     <- the ``*_ciderdf.pkl`` of ``compute_ciderdf.py``
 * :class:`RefSet`                      device-resident reference rows
+* :class:`HostRewardPipeline`          the same reward for pinned host batches (upload overlapped with scoring)
 
 Importing this package loads ``libcst_reward.so`` (hand-written CUDA for
 sm_100a behind the C ABI of ``include/cst_reward.h``) and fails if it has not
@@ -16,3 +17,4 @@ from ._lib import CstError, LIB_PATH, lib          # noqa: F401  (loads the .so)
 from .df_table import DfTable, pack_ngrams, unpack_keys  # noqa: F401
 from .ciderd import CiderD                          # noqa: F401
 from .reward import RefSet, get_cst_reward, get_self_critical_reward  # noqa: F401
+from .pipeline import HostRewardPipeline            # noqa: F401
