@@ -628,13 +628,20 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
     double* invn = reinterpret_cast<double*>(tab + p.tab_slots);   // [4][32]
     double* gh_all = invn + 128;                                    // [nwarps][2][32]
     double* sc = gh_all + nwarps * 64;                              // [n_local]
-    double* red = sc + n_local;                                     // [2 * nwarps]
+    double* low = sc + n_local;                                     // [cands_per_video]
+    double* red = low + p.cands_per_video;                          // [2 * nwarps]
     int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
     u32* tok_all = reinterpret_cast<u32*>(lenr + 32);               // [nwarps][32]
     double* gh = gh_all + warp * 64;
     u32* tokbuf = tok_all + warp * 32;
 
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
+#ifdef CST_PHASE_TIMING
+        long long tk0 = clock64(), tk1 = 0, tk2 = 0, tk3 = 0, tk4 = 0;
+#define CST_TICK(x) x = clock64()
+#else
+#define CST_TICK(x)
+#endif
         int64_t r0, r1;
         if (p.ref_offsets) {
             r0 = p.ref_offsets[video];
@@ -654,6 +661,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                 for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
             }
             __syncthreads();
+            CST_TICK(tk1);
             // ---- phase R: two reference rows per warp ----
             for (int base = 2 * warp; base < nref; base += 2 * nwarps) {
                 const RT* rows = reinterpret_cast<const RT*>(p.refs) + (c0 + base) * p.ref_stride;
@@ -673,6 +681,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                 }
             }
             __syncthreads();                         // the video table is complete
+            CST_TICK(tk2);
             // ---- phase C: two candidate rows per warp ----
             for (int base = 2 * warp; base < n_local; base += 2 * nwarps) {
                 const int c = base + sub;
@@ -703,38 +712,82 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                 }
             }
             __syncthreads();                         // all probes done before the table is cleared again
+            CST_TICK(tk3);
         }
         if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
         if (bad_rows && p.ctl) atomicAdd(&p.ctl[1], bad_rows);
 
-        // ---- phase B (warp 0): finish the scores, baseline, rewards, statistics ----
-        if (warp == 0) {
-            // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
-            for (int c = lane; c < n_local; c += 32) {
-                double s = sc[c] * 0.25;
-                s = (R > 0) ? s / (double)R : 0.0;
-                s *= 10.0;
-                sc[c] = s;
-                if (p.scores) {
-                    const bool is_greedy = c >= p.cands_per_video;
-                    const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
-                    p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
-                }
+        // ---- phase B, spread over the whole CTA (a lone warp would hold 9 idle ones) ----
+        // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
+        for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
+            double s = sc[c] * 0.25;
+            s = (R > 0) ? s / (double)R : 0.0;
+            s *= 10.0;
+            sc[c] = s;
+            if (p.scores) {
+                const bool is_greedy = c >= p.cands_per_video;
+                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
+                p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
             }
-            __syncwarp();
-            if (p.mode >= 0) {
-                const int S = p.cands_per_video;
-                const double* other = (p.mode == CST_BASE_GREEDY) ? (sc + S)
-                                      : (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : nullptr;
-                double sm, sb;
-                baseline_group(sc, other, S, p.mode, p.scb_k, lane, p.reward + video * S, sm, sb);
+        }
+        __syncthreads();
+        if (p.mode >= 0) {
+            const int S = p.cands_per_video;
+            const bool scb = (p.mode == CST_BASE_SCB_GT || p.mode == CST_BASE_SCB_SAMPLE);
+            const double* x = (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
+            if (scb) {
+                // k lowest of the row (utils.py:294-312): element i is ranked by one warp with
+                // ballots (ties by index = stable sort); low[i] = x_i if its rank < k
+                for (int i = warp; i < S; i += nwarps) {
+                    const double xi = x[i];
+                    int rank = 0;
+                    for (int j0 = 0; j0 < S; j0 += 32) {
+                        const int j = j0 + lane;
+                        const double xj = (j < S) ? x[j] : 0.0;
+                        rank += __popc(__ballot_sync(CST_FULL, j < S && (xj < xi || (xj == xi && j < i))));
+                    }
+                    if (lane == 0) low[i] = (rank < p.scb_k) ? xi : 0.0;
+                }
+                __syncthreads();
+            }
+            double lowsum = 0.0;
+            if (scb) {
+                for (int i = lane; i < S; i += 32) lowsum += low[i];
+                lowsum = warp_sum(lowsum);                       // same fixed tree in every warp
+            }
+            const double base = scb ? lowsum / (double)p.scb_k : 0.0;
+            for (int i = threadIdx.x; i < S; i += blockDim.x) {
+                const double r = (p.mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
+                p.reward[video * S + i] = (float)r;
+            }
+            if (warp == 0) {                                      // the video's share of the statistics
+                double am = 0.0, ab = 0.0;
+                for (int i = lane; i < S; i += 32) {
+                    am += sc[i];
+                    if (p.mode == CST_BASE_GREEDY) ab += sc[S + i];
+                    if (p.mode == CST_BASE_SCB_GT) ab += x[i];
+                }
+                am = warp_sum(am);
+                ab = warp_sum(ab);
+                if (p.mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
                 if (lane == 0) {
-                    p.partials[2 * video] = sm;
-                    p.partials[2 * video + 1] = sb;
+                    p.partials[2 * video] = am;
+                    p.partials[2 * video + 1] = ab;
                 }
             }
         }
         __syncthreads();
+#ifdef CST_PHASE_TIMING
+        CST_TICK(tk4);
+        if (p.ctl && (threadIdx.x & 31) == 0) {      // per warp: where its time went (cycles)
+            unsigned long long* t = reinterpret_cast<unsigned long long*>(p.ctl) + 8;
+            atomicAdd(t + 0, (unsigned long long)(tk1 - tk0));
+            atomicAdd(t + 1, (unsigned long long)(tk2 - tk1));
+            atomicAdd(t + 2, (unsigned long long)(tk3 - tk2));
+            atomicAdd(t + 3, (unsigned long long)(tk4 - tk3));
+            atomicAdd(t + 4, 1ull);
+        }
+#endif
     }
     if (p.mode >= 0) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
 }
@@ -879,7 +932,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (nwarps < 4) nwarps = 4;
     const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
                         (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
-                        (size_t)2 * nwarps * sizeof(double) +
+                        (size_t)cands_per_video * sizeof(double) + (size_t)2 * nwarps * sizeof(double) +
                         32 * sizeof(int) + (size_t)nwarps * 32 * sizeof(u32);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 

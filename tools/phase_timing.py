@@ -1,0 +1,31 @@
+"""Developer tool: average cycles a warp spends in each phase of k_score.
+Build the library with -DCST_PHASE_TIMING first (CST_NVCC_EXTRA=-DCST_PHASE_TIMING)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+import __graft_entry__ as g
+g.build()
+import cst_captioning_b200 as cst
+from cst_captioning_b200 import synth, reward
+dev = torch.device('cuda:0')
+rng = np.random.default_rng(synth.SEED)
+corpus, _ = synth.make_refs(rng, 6513, 20)
+scorer = cst.CiderD(df=cst.DfTable.from_rows(torch.from_numpy(corpus).to(dev), use_eos=1))
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
+b = synth.make_batch(n, 20, 20, seed=1000)
+c = torch.from_numpy(b['sampled']).to(dev)
+r = cst.RefSet(torch.from_numpy(b['refs']).to(dev).reshape(n * 20, 30), per_video=20)
+kw = dict(expand_feat=1, seq_per_img=20, scb_captions=20, scb_baseline=2, use_eos=1)
+for _ in range(3):
+    cst.get_cst_reward(c, r, scorer, **kw)
+torch.cuda.synchronize()
+scratch = reward._scratch[dev]
+t0 = scratch[64:64 + 40].clone().view(torch.int64).cpu().numpy()
+cst.get_cst_reward(c, r, scorer, **kw)
+torch.cuda.synchronize()
+t1 = scratch[64:64 + 40].clone().view(torch.int64).cpu().numpy()
+d = (t1 - t0).astype(np.float64)
+names = ['clear+wait', 'phase R (+barrier)', 'phase C (+barrier)', 'phase B']
+for nm, v in zip(names, d[:4] / d[4]):
+    print('%-22s %10.0f cycles per warp per video' % (nm, v))
+print('total %10.0f' % (d[:4].sum() / d[4]))
