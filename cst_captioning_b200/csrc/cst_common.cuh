@@ -183,10 +183,15 @@ __device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, 
 // to the row's lane group); the lowest lane of every set of equal keys is the leader
 // (the dict entry precook would create at that position).
 template <int G>
-__device__ __forceinline__ void row_tf(const u64 key[4], int lane, int tf[4], bool lead[4]) {
+__device__ __forceinline__ void row_tf(const u64 key[4], int lane, int only, int tf[4], bool lead[4]) {
     const u32 gm = Grp<G>::mask(lane);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
+        if (only >= 0 && k != only) {          // warp-uniform: this item covers a single order
+            tf[k] = 0;
+            lead[k] = false;
+            continue;
+        }
         const u32 m = __match_any_sync(CST_FULL, key[k]) & gm;
         tf[k] = __popc(m);
         lead[k] = (key[k] != 0ull) && ((__ffs(m) - 1) == lane);

@@ -325,7 +325,7 @@ __global__ void k_ngram_counts(const T* __restrict__ rows, int64_t n_rows, int w
     canon_row<T, 32>(rows + row * stride, width, use_eos, lane, tokbuf[warp], key, L);
     int tf[4];
     bool lead[4];
-    row_tf<32>(key, lane, tf, lead);
+    row_tf<32>(key, lane, -1, tf, lead);
     int base = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -501,19 +501,21 @@ struct ScoreParams {
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
 
 // Phase R for one reference row per lane group (G = 32: one row, G = 16: two rows of
-// this warp, one per half).  `width` = 0 marks an idle group (odd row count).
-// Returns the canonical length (so the caller can redo rows longer than G) and
-// whether the row held a bad id.
+// this warp, one per half).  `width` = 0 marks an idle group (odd row count).  With
+// G = 16 a row whose canonical length exceeds 16 tokens yields no keys and is left to
+// the long-row pass.  `only` >= 0 restricts the item to one n-gram order (the long-row
+// pass spreads the four orders of a row over four warps), -1 = all four.
+// Returns the canonical length.
 template <typename RT, int G>
-__device__ __forceinline__ int ref_phase(const ScoreParams& p, const RT* row, int width, int rl, int lane,
+__device__ __forceinline__ int ref_phase(const ScoreParams& p, const RT* row, int width, int rl, int lane, int only,
                                          VidSlot* tab, double* invn, int* lenr, u32* tokbuf, bool& bad) {
     u64 key[4];
     int L;
     bad = canon_row<RT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
-    if (G == 16 && __any_sync(CST_FULL, L > 16)) return L;      // warp-uniform: redo both rows with G = 32
+    const bool live = width > 0 && (G == 32 || L <= 16);
     int tf[4];
     bool lead[4];
-    row_tf<G>(key, lane, tf, lead);
+    row_tf<G>(key, lane, only, tf, lead);
     u32 h[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
@@ -541,27 +543,27 @@ __device__ __forceinline__ int ref_phase(const ScoreParams& p, const RT* row, in
         n2[k] = w * w;                                             // norm += vec ** 2
     }
     const double tot = group_sum4_transposed<G>(n2, lane);
-    if (width > 0) {
-        if ((lane & (G / 4 - 1)) == 0) invn[group_order<G>(lane) * 32 + rl] = inv_norm_of(tot);
-        if (Grp<G>::sl(lane) == 0) lenr[rl] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
+    if (live) {
+        const int o = group_order<G>(lane);
+        if ((lane & (G / 4 - 1)) == 0 && (only < 0 || o == only)) invn[o * 32 + rl] = inv_norm_of(tot);
+        if (Grp<G>::sl(lane) == 0 && only <= 0) lenr[rl] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
     }
     return L;
 }
 
 // Phase C for one candidate row per lane group: sum over the chunk's refs of
 // sum_n sim_n / (norm_h[n] norm_r[n]) * penalty  (not yet / n, / R, * 10), returned
-// in `score` on every lane of the group.
+// in `score` on every lane of the group (restricted to order `only` if >= 0).
 template <typename CT, int G>
-__device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, int width, int nref, int lane,
+__device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, int width, int nref, int lane, int only,
                                           const VidSlot* tab, const double* invn, const int* lenr, double* gh,
                                           u32* tokbuf, bool& bad, double& score) {
     u64 key[4];
     int L;
     bad = canon_row<CT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
-    if (G == 16 && __any_sync(CST_FULL, L > 16)) return L;
     int tf[4];
     bool lead[4];
-    row_tf<G>(key, lane, tf, lead);
+    row_tf<G>(key, lane, only, tf, lead);
     u32 h[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
@@ -618,6 +620,7 @@ __device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, i
 template <typename CT, typename RT>
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_nlong[2];                       // long rows met in phase R / phase C of the chunk
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
@@ -629,9 +632,12 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
     double* gh_all = invn + 128;                                    // [nwarps][2][32]
     double* sc = gh_all + nwarps * 64;                              // [n_local]
     double* low = sc + n_local;                                     // [cands_per_video]
-    double* red = low + p.cands_per_video;                          // [2 * nwarps]
+    double* part = low + p.cands_per_video;                         // [n_local][4] long-row partial scores
+    double* red = part + 4 * n_local;                               // [2 * nwarps]
     int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
-    u32* tok_all = reinterpret_cast<u32*>(lenr + 32);               // [nwarps][32]
+    int* long_r = lenr + 32;                                        // [32] long reference rows of the chunk
+    int* long_c = long_r + 32;                                      // [n_local] long candidate rows
+    u32* tok_all = reinterpret_cast<u32*>(long_c + n_local);        // [nwarps][32]
     double* gh = gh_all + warp * 64;
     u32* tokbuf = tok_all + warp * 32;
 
@@ -659,29 +665,41 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
             {   // clear the video table
                 uint4* z = reinterpret_cast<uint4*>(tab);
                 for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+                if (threadIdx.x < 2) s_nlong[threadIdx.x] = 0;
             }
             __syncthreads();
             CST_TICK(tk1);
             // ---- phase R: two reference rows per warp ----
+            const RT* ref0 = reinterpret_cast<const RT*>(p.refs) + c0 * p.ref_stride;
             for (int base = 2 * warp; base < nref; base += 2 * nwarps) {
-                const RT* rows = reinterpret_cast<const RT*>(p.refs) + (c0 + base) * p.ref_stride;
                 const int rl = base + sub;
                 const bool act = rl < nref;
                 bool bad;
-                const int L = ref_phase<RT, 16>(p, rows + (act ? sub : 0) * p.ref_stride, act ? p.ref_width : 0, rl,
-                                                lane, tab, invn, lenr, tokbuf, bad);
-                if (__any_sync(CST_FULL, L > 16)) {          // a long row: redo the pair one row per warp
-                    for (int q = 0; q < 2 && base + q < nref; ++q) {
-                        ref_phase<RT, 32>(p, rows + q * p.ref_stride, p.ref_width, base + q, lane, tab, invn, lenr,
-                                          tokbuf, bad);
-                        if (bad && lane == 0) ++bad_rows;
-                    }
-                } else if (bad && act && (lane & 15) == 0) {
-                    ++bad_rows;
+                const int L = ref_phase<RT, 16>(p, ref0 + (act ? rl : base) * p.ref_stride, act ? p.ref_width : 0, rl,
+                                                lane, -1, tab, invn, lenr, tokbuf, bad);
+                if (act && (lane & 15) == 0) {
+                    if (L > 16) long_r[atomicAdd(&s_nlong[0], 1)] = rl;      // left to the long-row pass
+                    else if (bad) ++bad_rows;
                 }
             }
-            __syncthreads();                         // the video table is complete
-            CST_TICK(tk2);
+            __syncthreads();
+            if (s_nlong[0] > 0) {
+                // long-row pass: one row per warp, or -- when few rows are long -- the four
+                // n-gram orders of a row on four warps, so the pass is short for everyone
+                const int nl = s_nlong[0];
+                const bool split = nl * 2 <= nwarps;
+                const int items = split ? nl * 4 : nl;
+                for (int it = warp; it < items; it += nwarps) {
+                    const int rl = long_r[split ? (it >> 2) : it];
+                    const int only = split ? (it & 3) : -1;
+                    bool bad;
+                    ref_phase<RT, 32>(p, ref0 + rl * p.ref_stride, p.ref_width, rl, lane, only, tab, invn, lenr,
+                                      tokbuf, bad);
+                    if (bad && lane == 0 && only <= 0) ++bad_rows;
+                }
+                __syncthreads();
+            }
+            CST_TICK(tk2);                               // the video table is complete
             // ---- phase C: two candidate rows per warp ----
             for (int base = 2 * warp; base < n_local; base += 2 * nwarps) {
                 const int c = base + sub;
@@ -692,26 +710,47 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScorePara
                 const CT* row = reinterpret_cast<const CT*>(is_greedy ? p.greedy : p.cand) + ci * p.cand_stride;
                 bool bad;
                 double t = 0.0;
-                const int L = cand_phase<CT, 16>(p, row, act ? p.cand_width : 0, nref, lane, tab, invn, lenr, gh,
+                const int L = cand_phase<CT, 16>(p, row, act ? p.cand_width : 0, nref, lane, -1, tab, invn, lenr, gh,
                                                  tokbuf, bad, t);
-                if (__any_sync(CST_FULL, L > 16)) {
-                    for (int q = 0; q < 2 && base + q < n_local; ++q) {
-                        const int cq = base + q;
-                        const bool gq = cq >= p.cands_per_video;
-                        const int64_t cqi = video * p.cands_per_video + (gq ? cq - p.cands_per_video : cq);
-                        const CT* rq = reinterpret_cast<const CT*>(gq ? p.greedy : p.cand) + cqi * p.cand_stride;
-                        cand_phase<CT, 32>(p, rq, p.cand_width, nref, lane, tab, invn, lenr, gh, tokbuf, bad, t);
-                        if (lane == 0) {
-                            sc[cq] += t;
-                            if (bad && c0 == r0) ++bad_rows;
-                        }
+                if (act && (lane & 15) == 0) {
+                    if (L > 16) {
+                        long_c[atomicAdd(&s_nlong[1], 1)] = c;
+                    } else {
+                        sc[c] += t;
+                        if (bad && c0 == r0) ++bad_rows;
                     }
-                } else if (act && (lane & 15) == 0) {
-                    sc[c] += t;
-                    if (bad && c0 == r0) ++bad_rows;
                 }
             }
-            __syncthreads();                         // all probes done before the table is cleared again
+            __syncthreads();
+            if (s_nlong[1] > 0) {
+                const int nl = s_nlong[1];
+                const bool split = nl * 2 <= nwarps;
+                const int items = split ? nl * 4 : nl;
+                for (int it = warp; it < items; it += nwarps) {
+                    const int slot = split ? (it >> 2) : it;
+                    const int only = split ? (it & 3) : -1;
+                    const int cq = long_c[slot];
+                    const bool gq = cq >= p.cands_per_video;
+                    const int64_t cqi = video * p.cands_per_video + (gq ? cq - p.cands_per_video : cq);
+                    const CT* rq = reinterpret_cast<const CT*>(gq ? p.greedy : p.cand) + cqi * p.cand_stride;
+                    bool bad;
+                    double t = 0.0;
+                    cand_phase<CT, 32>(p, rq, p.cand_width, nref, lane, only, tab, invn, lenr, gh, tokbuf, bad, t);
+                    if (lane == 0) {
+                        if (split) {
+                            part[4 * slot + only] = t;
+                        } else {
+                            part[4 * slot] = t;
+                            part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
+                        }
+                        if (bad && c0 == r0 && only <= 0) ++bad_rows;
+                    }
+                }
+                __syncthreads();
+                for (int i = threadIdx.x; i < nl; i += blockDim.x)       // fixed order: deterministic
+                    sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
+                __syncthreads();                         // all probes done before the table is cleared again
+            }
             CST_TICK(tk3);
         }
         if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
@@ -932,8 +971,9 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (nwarps < 4) nwarps = 4;
     const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
                         (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
-                        (size_t)cands_per_video * sizeof(double) + (size_t)2 * nwarps * sizeof(double) +
-                        32 * sizeof(int) + (size_t)nwarps * 32 * sizeof(u32);
+                        (size_t)cands_per_video * sizeof(double) + (size_t)4 * n_local * sizeof(double) +
+                        (size_t)2 * nwarps * sizeof(double) + (64 + (size_t)n_local) * sizeof(int) +
+                        (size_t)nwarps * 32 * sizeof(u32);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 
     const int threads = nwarps * 32;
@@ -1060,7 +1100,7 @@ __global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, in
             if (bad && lane == 0) atomicAdd(n_bad, 1u);
             int tf[4];
             bool lead[4];
-            row_tf<32>(key, lane, tf, lead);
+            row_tf<32>(key, lane, -1, tf, lead);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 if (!lead[k]) continue;
