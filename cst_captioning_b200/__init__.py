@@ -7,6 +7,7 @@ Public surface (mirrors the reference's interfaces for this path):
 * :func:`get_self_critical_reward`     <- ``utils.get_self_critical_reward`` (``utils.py:169``)
 * :class:`DfTable`                     <- the ``*_ciderdf.pkl`` of ``compute_ciderdf.py``
 * :class:`RefSet`                      device-resident reference rows
+* :class:`RewardCriterion`             <- ``model.RewardCriterion`` (``model.py:7-23``), fused fwd/bwd
 * :class:`HostRewardPipeline`          the same reward for pinned host batches (upload overlapped with scoring)
 
 Importing this package loads ``libcst_reward.so`` (hand-written CUDA for
@@ -18,3 +19,4 @@ from .df_table import DfTable, pack_ngrams, unpack_keys  # noqa: F401
 from .ciderd import CiderD                          # noqa: F401
 from .reward import RefSet, get_cst_reward, get_self_critical_reward  # noqa: F401
 from .pipeline import HostRewardPipeline            # noqa: F401
+from .criterion import RewardCriterion              # noqa: F401

@@ -42,6 +42,11 @@ SYMBOLS = {
     'cst_reward_scratch_bytes': (_i64, [_i64]),
     'cst_reward': (C.c_int, [_vp] + _ROWS + [_i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     'cst_reward_noalloc': (C.c_int, [_vp] + _ROWS + [_i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    'cst_criterion_scratch_bytes': (_i64, []),
+    'cst_reward_criterion_fwd': (C.c_int, [_vp, _i32, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _i64,
+                                           C.c_int, _vp]),
+    'cst_reward_criterion_bwd': (C.c_int, [_vp, _i32, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _i32, _vp, _i64, C.c_int,
+                                           _vp]),
     'cst_scb_apply': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _i64, C.c_int, _vp]),
 }
 

@@ -1,0 +1,202 @@
+// Fused consumer of the reward: the policy-gradient loss of model.py:7-23
+// (RewardCriterion) and its gradient, taking the per-caption reward column directly
+// so the (N, T) broadcast of utils.py:224,322 is never materialised.
+//
+//   mask[i][0] = 1, mask[i][t] = (seq[i][t-1] > 0)          (model.py:15-18)
+//   loss = sum(-logp * reward * mask) / sum(mask)            (model.py:20-21)
+//   dloss/dlogp[i][t] = -reward[i] * mask[i][t] / sum(mask)
+//
+// Both kernels stream their inputs once: HBM-bound by construction (per token 8 B of
+// int64 seq + 4 B of logp read; the backward also writes 4 B).
+#include <stdint.h>
+
+#include "cst_common.cuh"
+#include "cst_internal.h"
+#include "cst_reward.h"
+
+#define CRIT_THREADS 256
+#define CRIT_ROWS_PER_ITER 4      /* independent rows in flight per warp */
+
+template <typename ST>
+__device__ __forceinline__ bool tok_positive(const ST* seq_row, int t) {
+    return t == 0 || __ldcs(seq_row + (t - 1)) > 0;
+}
+
+__device__ __forceinline__ double crit_warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(CST_FULL, v, o);
+    return v;
+}
+
+// One warp per row, lane = column (T <= 32 per pass, wider rows loop).  Per-CTA partial
+// sums go to scratch; the last CTA adds them in a fixed order (deterministic loss).
+template <typename ST>
+__global__ void __launch_bounds__(CRIT_THREADS) k_criterion_fwd(
+    const ST* __restrict__ seq, int64_t seq_stride, const float* __restrict__ logp, int64_t logp_stride,
+    const float* __restrict__ reward, int64_t reward_row_stride, int64_t reward_col_stride, int64_t n_rows, int width,
+    float* loss_out, float* den_out, u32* ctl, double* partials) {
+    __shared__ double s_red[2 * (CRIT_THREADS / 32)];
+    __shared__ int s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t warps_total = (int64_t)gridDim.x * (CRIT_THREADS / 32);
+    const int64_t gw = (int64_t)blockIdx.x * (CRIT_THREADS / 32) + warp;
+    double num = 0.0, den = 0.0;
+    for (int64_t r0 = gw * CRIT_ROWS_PER_ITER; r0 < n_rows; r0 += warps_total * CRIT_ROWS_PER_ITER) {
+#pragma unroll
+        for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+            const int64_t i = r0 + q;
+            if (i >= n_rows) break;
+            for (int t = lane; t < width; t += 32) {
+                const bool m = tok_positive(seq + i * seq_stride, t);
+                const float lp = __ldcs(logp + i * logp_stride + t);
+                const float rw = __ldg(reward + i * reward_row_stride + t * reward_col_stride);
+                if (m) {
+                    num += (double)(-lp * rw);
+                    den += 1.0;
+                }
+            }
+        }
+    }
+    num = crit_warp_sum(num);
+    den = crit_warp_sum(den);
+    if (lane == 0) {
+        s_red[2 * warp] = num;
+        s_red[2 * warp + 1] = den;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < CRIT_THREADS / 32; ++w) {
+            a += s_red[2 * w];
+            b += s_red[2 * w + 1];
+        }
+        partials[2 * blockIdx.x] = a;
+        partials[2 * blockIdx.x + 1] = b;
+        __threadfence();
+        s_last = (atomicAdd(&ctl[0], 1u) == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double a = 0.0, b = 0.0;
+    for (int g = threadIdx.x; g < (int)gridDim.x; g += CRIT_THREADS) {
+        a += __ldcg(partials + 2 * g);
+        b += __ldcg(partials + 2 * g + 1);
+    }
+    a = crit_warp_sum(a);
+    b = crit_warp_sum(b);
+    __syncthreads();
+    if (lane == 0) {
+        s_red[2 * warp] = a;
+        s_red[2 * warp + 1] = b;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double ta = 0.0, tb = 0.0;
+        for (int w = 0; w < CRIT_THREADS / 32; ++w) {
+            ta += s_red[2 * w];
+            tb += s_red[2 * w + 1];
+        }
+        *loss_out = (float)(ta / tb);
+        *den_out = (float)tb;
+        ctl[0] = 0u;
+    }
+}
+
+template <typename ST>
+__global__ void __launch_bounds__(CRIT_THREADS) k_criterion_bwd(
+    const ST* __restrict__ seq, int64_t seq_stride, const float* __restrict__ reward, int64_t reward_row_stride,
+    int64_t reward_col_stride, const float* __restrict__ den, const float* __restrict__ grad_out, int64_t n_rows,
+    int width, float* grad_logp, int64_t grad_stride) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t warps_total = (int64_t)gridDim.x * (CRIT_THREADS / 32);
+    const int64_t gw = (int64_t)blockIdx.x * (CRIT_THREADS / 32) + warp;
+    const float scale = -(*grad_out) / (*den);
+    for (int64_t r0 = gw * CRIT_ROWS_PER_ITER; r0 < n_rows; r0 += warps_total * CRIT_ROWS_PER_ITER) {
+#pragma unroll
+        for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+            const int64_t i = r0 + q;
+            if (i >= n_rows) break;
+            for (int t = lane; t < width; t += 32) {
+                const bool m = tok_positive(seq + i * seq_stride, t);
+                const float rw = __ldg(reward + i * reward_row_stride + t * reward_col_stride);
+                __stcs(grad_logp + i * grad_stride + t, m ? scale * rw : 0.0f);
+            }
+        }
+    }
+}
+
+static int crit_grid(int64_t n_rows) {
+    int64_t want = (n_rows + (CRIT_THREADS / 32) * CRIT_ROWS_PER_ITER - 1) / ((CRIT_THREADS / 32) * CRIT_ROWS_PER_ITER);
+    const int64_t cap = 148 * 8;      // 8 resident CTAs of 256 threads per SM
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return (int)want;
+}
+
+extern "C" int64_t cst_criterion_scratch_bytes(void) { return 256 + 16 * 148 * 8; }
+
+static int crit_check(const char* who, const void* seq, int32_t seq_dtype, const void* reward, int64_t n_rows,
+                      int32_t width, int64_t seq_stride) {
+    if (n_rows < 0 || width < 1) return cst_fail(CST_E_ARG, "%s: bad shape", who);
+    if (seq_dtype != CST_DTYPE_I32 && seq_dtype != CST_DTYPE_I64) return cst_fail(CST_E_ARG, "%s: bad seq dtype", who);
+    if (n_rows > 0 && (!seq || !reward)) return cst_fail(CST_E_ARG, "%s: NULL input", who);
+    if (seq_stride < width) return cst_fail(CST_E_ARG, "%s: seq stride < width", who);
+    return CST_OK;
+}
+
+extern "C" int cst_reward_criterion_fwd(const void* seq, int32_t seq_dtype, int64_t seq_stride, const float* logprobs,
+                                        int64_t logp_stride, const float* reward, int64_t reward_row_stride,
+                                        int64_t reward_col_stride, int64_t n_rows, int32_t width, float* loss_out,
+                                        float* den_out, void* scratch, int64_t scratch_bytes, int device,
+                                        void* stream) {
+    int rc = crit_check("cst_reward_criterion_fwd", seq, seq_dtype, reward, n_rows, width, seq_stride);
+    if (rc != CST_OK) return rc;
+    if (n_rows == 0) return cst_fail(CST_E_ARG, "cst_reward_criterion_fwd: empty batch (the loss would be 0/0)");
+    if (!logprobs || !loss_out || !den_out) return cst_fail(CST_E_ARG, "cst_reward_criterion_fwd: NULL argument");
+    if (!scratch || scratch_bytes < cst_criterion_scratch_bytes())
+        return cst_fail(CST_E_ARG, "cst_reward_criterion_fwd: scratch too small");
+    CstDeviceGuard guard(device);
+    if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_reward_criterion_fwd: cannot select device %d", device);
+    u32* ctl = reinterpret_cast<u32*>(scratch);
+    double* partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
+    const int grid = crit_grid(n_rows);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (seq_dtype == CST_DTYPE_I64)
+        k_criterion_fwd<int64_t><<<grid, CRIT_THREADS, 0, st>>>((const int64_t*)seq, seq_stride, logprobs, logp_stride,
+                                                                 reward, reward_row_stride, reward_col_stride, n_rows,
+                                                                 width, loss_out, den_out, ctl, partials);
+    else
+        k_criterion_fwd<int32_t><<<grid, CRIT_THREADS, 0, st>>>((const int32_t*)seq, seq_stride, logprobs, logp_stride,
+                                                                 reward, reward_row_stride, reward_col_stride, n_rows,
+                                                                 width, loss_out, den_out, ctl, partials);
+    cst_count_launch();
+    CST_CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+extern "C" int cst_reward_criterion_bwd(const void* seq, int32_t seq_dtype, int64_t seq_stride, const float* reward,
+                                        int64_t reward_row_stride, int64_t reward_col_stride, const float* den,
+                                        const float* grad_out, int64_t n_rows, int32_t width, float* grad_logprobs,
+                                        int64_t grad_stride, int device, void* stream) {
+    int rc = crit_check("cst_reward_criterion_bwd", seq, seq_dtype, reward, n_rows, width, seq_stride);
+    if (rc != CST_OK) return rc;
+    if (n_rows == 0) return CST_OK;
+    if (!den || !grad_out || !grad_logprobs) return cst_fail(CST_E_ARG, "cst_reward_criterion_bwd: NULL argument");
+    if (grad_stride < width) return cst_fail(CST_E_ARG, "cst_reward_criterion_bwd: grad stride < width");
+    CstDeviceGuard guard(device);
+    if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_reward_criterion_bwd: cannot select device %d", device);
+    const int grid = crit_grid(n_rows);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (seq_dtype == CST_DTYPE_I64)
+        k_criterion_bwd<int64_t><<<grid, CRIT_THREADS, 0, st>>>((const int64_t*)seq, seq_stride, reward,
+                                                                 reward_row_stride, reward_col_stride, den, grad_out,
+                                                                 n_rows, width, grad_logprobs, grad_stride);
+    else
+        k_criterion_bwd<int32_t><<<grid, CRIT_THREADS, 0, st>>>((const int32_t*)seq, seq_stride, reward,
+                                                                 reward_row_stride, reward_col_stride, den, grad_out,
+                                                                 n_rows, width, grad_logprobs, grad_stride);
+    cst_count_launch();
+    CST_CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}

@@ -23,6 +23,7 @@
 #include <vector>
 
 #include "cst_common.cuh"
+#include "cst_internal.h"
 #include "cst_reward.h"
 
 // ---------------------------------------------------------------------------
@@ -52,6 +53,16 @@ extern "C" int cst_abi_version(void) { return 1; }
 static std::atomic<long long> g_launches{0};
 #define COUNT_LAUNCH() g_launches.fetch_add(1, std::memory_order_relaxed)
 extern "C" int64_t cst_kernel_launches(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
+
+// entry points of cst_internal.h for the other translation units
+int cst_fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+void cst_count_launch(void) { COUNT_LAUNCH(); }
 
 struct DeviceGuard {
     int prev = -1;

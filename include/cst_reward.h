@@ -241,6 +241,32 @@ int cst_scb_apply(const double* scores, const double* other, int64_t n_rows,
                   float* reward_out, double* stats_out, void* scratch,
                   int64_t scratch_bytes, int device, void* stream);
 
+/* ---- fused consumer of the reward -------------------------------
+ * Replaces RewardCriterion.forward (model.py:12-23) and its autograd backward as
+ * called at train.py:206-210: loss = sum(-logprobs * reward * mask) / sum(mask) with
+ * mask[i][0] = 1, mask[i][t] = (seq[i][t-1] > 0).  The reward is read through two
+ * strides, so the per-caption column of cst_reward (row stride 1, column stride 0) is
+ * consumed directly and the (N, T) broadcast of utils.py:224,322 never exists; a full
+ * (N, T) reward works too.  seq [dev] int32/int64 (n_rows, width), logprobs [dev]
+ * float32, loss_out / den_out [dev] one float each (den = sum(mask), kept for the
+ * backward).  Scratch as for cst_reward: cst_criterion_scratch_bytes() bytes, zeroed
+ * once.  Deterministic. */
+int64_t cst_criterion_scratch_bytes(void);
+int cst_reward_criterion_fwd(const void* seq, int32_t seq_dtype, int64_t seq_stride,
+                             const float* logprobs, int64_t logp_stride,
+                             const float* reward, int64_t reward_row_stride,
+                             int64_t reward_col_stride, int64_t n_rows, int32_t width,
+                             float* loss_out, float* den_out, void* scratch,
+                             int64_t scratch_bytes, int device, void* stream);
+/* grad_logprobs[i][t] = -grad_out * reward[i][t] * mask[i][t] / den (what autograd
+ * derives from model.py:20-21); grad_out [dev] is the scalar upstream gradient. */
+int cst_reward_criterion_bwd(const void* seq, int32_t seq_dtype, int64_t seq_stride,
+                             const float* reward, int64_t reward_row_stride,
+                             int64_t reward_col_stride, const float* den,
+                             const float* grad_out, int64_t n_rows, int32_t width,
+                             float* grad_logprobs, int64_t grad_stride, int device,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif
