@@ -353,7 +353,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--videos', type=int, default=65536, help='videos per GPU per step')
-    ap.add_argument('--cpu-videos', type=int, default=160, help='CPU-baseline sample size (videos)')
+    ap.add_argument('--cpu-videos', type=int, default=640, help='CPU-baseline sample size (videos)')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--e2e-slices', type=int, default=16, help='video slices of the host pipeline')
     args = ap.parse_args()

@@ -31,20 +31,8 @@
 // ---------------------------------------------------------------------------
 static thread_local char g_err[512] = "";
 
-static int fail(int code, const char* fmt, ...) {
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(g_err, sizeof(g_err), fmt, ap);
-    va_end(ap);
-    return code;
-}
-
-#define CUDA_TRY(expr)                                                                 \
-    do {                                                                               \
-        cudaError_t e_ = (expr);                                                       \
-        if (e_ != cudaSuccess)                                                         \
-            return fail(CST_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));   \
-    } while (0)
+#define fail cst_fail
+#define CUDA_TRY CST_CUDA_TRY
 
 extern "C" const char* cst_last_error(void) { return g_err; }
 extern "C" int cst_abi_version(void) { return 1; }
@@ -64,17 +52,7 @@ int cst_fail(int code, const char* fmt, ...) {
 }
 void cst_count_launch(void) { COUNT_LAUNCH(); }
 
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = false;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) return;
-        ok = (prev == dev) || (cudaSetDevice(dev) == cudaSuccess);
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
+typedef CstDeviceGuard DeviceGuard;
 
 // ---------------------------------------------------------------------------
 // df table handle (layout: DfView in cst_common.cuh)
