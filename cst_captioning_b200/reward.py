@@ -129,7 +129,7 @@ def _launch_reward(scorer, sampled, greedy, refs, cands_per_video, use_eos, mode
     if n_videos * cands_per_video != n or n_videos > refs.n_videos:
         raise ValueError('caption count %d does not match %d videos x %d' % (n, refs.n_videos, cands_per_video))
     reward = torch.empty(n, dtype=torch.float32, device=dev)
-    stats = torch.empty(_lib.N_STATS, dtype=torch.float64, device=dev)
+    stats = (torch.zeros if n == 0 else torch.empty)(_lib.N_STATS, dtype=torch.float64, device=dev)
     fused = cands_per_video == seq_per_img
     scores = None
     if want_scores or not fused:
