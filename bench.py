@@ -21,10 +21,19 @@ import time
 
 import numpy as np
 
-os.environ.setdefault('NCCL_DEBUG_FILE', '/dev/stderr')   # stdout carries the one JSON line only
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+
+# stdout carries the ONE JSON line and nothing else: library chatter (NCCL prints its
+# version to stdout) is sent to stderr by pointing fd 1 there for the whole run.
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_JSON_FD, (json.dumps(line) + '\n').encode())
+
 
 METRIC = 'cider_d_reward_captions_per_sec_20refs'
 UNIT = 'captions/s'
@@ -199,7 +208,7 @@ def reference_arm(args):
         'note': 'oracle port of utils.get_cst_reward + restated CiderD (the scorer is an absent, unpinned '
                 'dependency of the reference; nothing to compile into oracle/_ref)',
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -340,7 +349,7 @@ def product_arm(args):
             'check': {'m_score': float(stats[0] / stats[2]), 'b_score': float(stats[1] / stats[3]),
                       'bad_rows': float(stats[4]), 'df_ngrams': len(table)},
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
