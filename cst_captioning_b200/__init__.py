@@ -17,6 +17,6 @@ been built: there is no CPU fallback.
 from ._lib import CstError, LIB_PATH, lib          # noqa: F401  (loads the .so)
 from .df_table import DfTable, pack_ngrams, unpack_keys  # noqa: F401
 from .ciderd import CiderD                          # noqa: F401
-from .reward import RefSet, get_cst_reward, get_self_critical_reward  # noqa: F401
+from .reward import RefSet, RefStore, get_cst_reward, get_self_critical_reward  # noqa: F401
 from .pipeline import HostRewardPipeline            # noqa: F401
 from .criterion import RewardCriterion              # noqa: F401

@@ -79,6 +79,37 @@ class RefSet:
         return cls.from_list(data_gts, device)
 
 
+class RefStore:
+    """The whole label matrix kept on the device.
+
+    The reference's loader re-reads the references of every batch video from HDF5 and
+    ships them to the reward function on the host (``dataloader.py:119-139``: rows
+    ``label_start_ix[v]:label_end_ix[v]`` of ``labels``).  Upload ``labels`` once,
+    then a training step passes only its video indices: ``store.batch(ids)`` gathers
+    the rows on the device into a :class:`RefSet`.
+    """
+
+    def __init__(self, labels, start_ix, end_ix, device=None):
+        t = labels if torch.is_tensor(labels) else torch.from_numpy(_narrow(np.ascontiguousarray(labels, np.int64)))
+        self.labels = t.to(device if device is not None else 'cuda').contiguous()
+        self.start = np.ascontiguousarray(start_ix, dtype=np.int64)
+        self.end = np.ascontiguousarray(end_ix, dtype=np.int64)
+        if self.start.shape != self.end.shape or np.any(self.end < self.start):
+            raise ValueError('start_ix / end_ix must pair up with end >= start')
+        if len(self.end) and self.end.max() > self.labels.shape[0]:
+            raise ValueError('end_ix beyond the label matrix')
+
+    def batch(self, video_ids):
+        ids = np.ascontiguousarray(video_ids, dtype=np.int64)
+        counts = self.end[ids] - self.start[ids]
+        offsets = np.concatenate([[0], np.cumsum(counts)])
+        rows = np.repeat(self.start[ids] - offsets[:-1], counts) + np.arange(offsets[-1])
+        picked = self.labels.index_select(0, torch.from_numpy(rows).to(self.labels.device))
+        if len(counts) and np.all(counts == counts[0]):
+            return RefSet(picked, per_video=int(counts[0]))
+        return RefSet(picked, offsets=offsets)
+
+
 def _narrow(rows):
     """Host int64 rows -> int32 when every id fits (halves the upload; ids outside
     [0, 65534] are rejected by the kernels either way)."""
