@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libcst_reward.so')
+# CST_REWARD_LIB: developer override to load an experimental build of the same ABI
+LIB_PATH = os.environ.get('CST_REWARD_LIB') or os.path.join(_HERE, 'libcst_reward.so')
 
 OK, E_ARG, E_CUDA, E_NOMEM, E_RANGE = 0, -1, -2, -3, -4
 DTYPE_I32, DTYPE_I64 = 0, 1

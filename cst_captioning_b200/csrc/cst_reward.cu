@@ -488,6 +488,9 @@ struct ScoreParams {
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
+#ifndef CST_MIN_CTAS
+#define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
+#endif
 
 // Phase R for one reference row per lane group (G = 32: one row, G = 16: two rows of
 // this warp, one per half).  `width` = 0 marks an idle group (odd row count).  With
@@ -607,7 +610,7 @@ __device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, i
 }
 
 template <typename CT, typename RT>
-__global__ void __launch_bounds__(CST_MAX_WARPS * 32, 4) k_score(const ScoreParams p) {
+__global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // long rows met in phase R / phase C of the chunk
     const int lane = threadIdx.x & 31;
