@@ -18,10 +18,11 @@ _scratch = {}
 
 
 def _scratch_for(device):
-    buf = _scratch.get(device)
+    key = (device, torch.cuda.current_stream(device).cuda_stream)     # never shared by overlapping launches
+    buf = _scratch.get(key)
     if buf is None:
         buf = torch.zeros(int(lib.cst_criterion_scratch_bytes()), dtype=torch.uint8, device=device)
-        _scratch[device] = buf
+        _scratch[key] = buf
     return buf
 
 

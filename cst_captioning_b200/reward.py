@@ -139,12 +139,14 @@ _scratch = {}
 
 
 def _scratch_for(device, n_groups):
-    """Zero-initialised scratch the kernels leave clean (see cst_reward_scratch_bytes)."""
+    """Zero-initialised scratch the kernels leave clean (see cst_reward_scratch_bytes).
+    One buffer per (device, stream): launches that may overlap never share one."""
     need = int(lib.cst_reward_scratch_bytes(n_groups))
-    buf = _scratch.get(device)
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    buf = _scratch.get(key)
     if buf is None or buf.numel() < need:
         buf = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=device)
-        _scratch[device] = buf
+        _scratch[key] = buf
     return buf
 
 

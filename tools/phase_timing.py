@@ -19,7 +19,7 @@ kw = dict(expand_feat=1, seq_per_img=20, scb_captions=20, scb_baseline=2, use_eo
 for _ in range(3):
     cst.get_cst_reward(c, r, scorer, **kw)
 torch.cuda.synchronize()
-scratch = reward._scratch[dev]
+scratch = reward._scratch[(dev, torch.cuda.current_stream(dev).cuda_stream)]
 t0 = scratch[64:64 + 40].clone().view(torch.int64).cpu().numpy()
 cst.get_cst_reward(c, r, scorer, **kw)
 torch.cuda.synchronize()
