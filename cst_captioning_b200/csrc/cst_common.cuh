@@ -102,65 +102,66 @@ __device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u;
 // Row canonicalisation + n-gram keys.  A row is handled by a group of G lanes:
 // G = 32 (one row per warp) or G = 16 (two rows per warp, one per half -- captions
 // average 11 tokens, so half-warps double the useful lanes; rows whose canonical
-// length exceeds 16 are redone with G = 32 by the caller).  `sl` = lane within the
-// group = n-gram start position, `sub` = which half.
+// length exceeds 16 yield no keys with G = 16 and are redone with G = 32 by the
+// caller).  G and the token width are RUN-TIME values on purpose: one copy of this
+// code serves references, candidates, both group sizes and both token types, which
+// keeps the scoring kernel small enough for the instruction cache (the first versions,
+// specialised four ways, were instruction-fetch bound).
 // Restates utils.py:135-152 (array_to_str) and compute_ciderdf.py:28-33
 // (precook's k/i loops) on packed keys.
-//   key[k]   packed (k+1)-gram starting at position sl, 0 if none
+//   key[k]   packed (k+1)-gram starting at the lane's position, 0 if none
 //   L        canonical token count of the group's row
 //   returns  true if the row held an id outside [-1, 65534] before its end
 // tokbuf: 32 u32 of warp-private shared memory (G = 16: 16 per half).
 // ---------------------------------------------------------------------------
-template <int G>
-struct Grp {
-    static_assert(G == 16 || G == 32, "row group is a warp or a half-warp");
-    __device__ static __forceinline__ int sub(int lane) { return G == 32 ? 0 : (lane >> 4); }
-    __device__ static __forceinline__ int sl(int lane) { return G == 32 ? lane : (lane & 15); }
-    __device__ static __forceinline__ u32 mask(int lane) { return G == 32 ? CST_FULL : (0xffffu << (lane & 16)); }
-    // 32-bit mask over the row's (up to 32) raw positions: pa speaks for position sl,
-    // pb for position sl + 16 (G = 16 only; each lane holds two raw tokens there).
-    __device__ static __forceinline__ u32 vote(bool pa, bool pb, int lane) {
-        const u32 a = __ballot_sync(CST_FULL, pa);
-        if (G == 32) return a;
-        const u32 b = __ballot_sync(CST_FULL, pb);
-        const int sh = lane & 16;
-        return ((a >> sh) & 0xffffu) | (((b >> sh) & 0xffffu) << 16);
-    }
-};
-
-template <typename T>
-__device__ __forceinline__ long long ld_tok(const T* p) {
-    return (long long)__ldcs(p);          // rows stream through once: evict-first
+__device__ __forceinline__ int grp_sl(int lane, int G) { return lane & (G - 1); }      // position in the group
+__device__ __forceinline__ int grp_shift(int lane, int G) { return lane & (32 - G); }  // first lane of the group
+__device__ __forceinline__ u32 grp_mask(int lane, int G) {
+    return (G == 32) ? CST_FULL : (0xffffu << grp_shift(lane, G));
+}
+// 32-bit mask over the row's (up to 32) raw positions: pa speaks for position sl, pb
+// for position sl + 16 (G = 16 only; each lane holds two raw tokens there).
+__device__ __forceinline__ u32 grp_vote(bool pa, bool pb, int lane, int G) {
+    const u32 a = __ballot_sync(CST_FULL, pa);
+    const u32 b = __ballot_sync(CST_FULL, pb);
+    const int sh = grp_shift(lane, G);
+    return (G == 32) ? a : (((a >> sh) & 0xffffu) | (((b >> sh) & 0xffffu) << 16));
 }
 
-template <typename T, int G>
-__device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, int use_eos, int lane,
+// token `i` of a row of int32 or int64 ids; rows stream through once: evict-first
+__device__ __forceinline__ long long ld_tok(const void* row, int is64, int i) {
+    return is64 ? (long long)__ldcs(reinterpret_cast<const long long*>(row) + i)
+                : (long long)__ldcs(reinterpret_cast<const int*>(row) + i);
+}
+
+__device__ __forceinline__ bool canon_row(const void* row, int is64, int width, int use_eos, int lane, int G,
                                           u32* tokbuf, u64 key[4], int& L) {
-    typedef Grp<G> Gp;
-    const int sl = Gp::sl(lane);
+    const int sl = grp_sl(lane, G);
+    const bool half = (G == 16);
     const int pa = sl, pb = sl + 16;                       // raw positions this lane owns
     const bool ina = pa < width;
-    const bool inb = (G == 16) && pb < width;
-    const long long ta = ina ? ld_tok(row + pa) : 0ll;
-    const long long tb = inb ? ld_tok(row + pb) : 0ll;
+    const bool inb = half && pb < width;
+    const long long ta = ina ? ld_tok(row, is64, pa) : 0ll;
+    const long long tb = inb ? ld_tok(row, is64, pb) : 0ll;
     const bool bada = ina && (ta < -1 || ta > 65534);
     const bool badb = inb && (tb < -1 || tb > 65534);
     // -1 = padding: ends the row, never emitted
-    const u32 tmask = Gp::vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane);
-    const u32 bmask = Gp::vote(bada, badb, lane);
+    const u32 tmask = grp_vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane, G);
+    const u32 bmask = grp_vote(bada, badb, lane, G);
     const int end = tmask ? (__ffs(tmask) - 1) : width;    // first <end> (or bad id), else row width
     const u32 upto_end = (end >= 31) ? CST_FULL : ((2u << end) - 1u);
     const bool keepa = (pa < end && ta != 1) || (use_eos && pa == end && ina && ta == 0);
-    const bool keepb = (G == 16) && ((pb < end && tb != 1) || (use_eos && pb == end && inb && tb == 0));
-    const u32 kmask = Gp::vote(keepa, keepb, lane);
+    const bool keepb = half && ((pb < end && tb != 1) || (use_eos && pb == end && inb && tb == 0));
+    const u32 kmask = grp_vote(keepa, keepb, lane, G);
     L = __popc(kmask);
-    u32* buf = tokbuf + Gp::sub(lane) * 16;
-    if (G == 32 || L <= 16) {                              // G = 16: longer rows are redone by the caller
+    const bool fits = L <= G;                              // G = 16: longer rows are redone by the caller
+    u32* buf = tokbuf + (grp_shift(lane, G) & 16);
+    if (fits) {
         if (keepa) buf[__popc(kmask & lanemask_lt(pa))] = (u32)ta + 1u;
         if (keepb) buf[__popc(kmask & lanemask_lt(pb))] = (u32)tb + 1u;
     }
     __syncwarp();
-    const u32 e0 = (sl < L && (G == 32 || L <= 16)) ? buf[sl] : 0u;
+    const u32 e0 = (sl < L && fits) ? buf[sl] : 0u;
     __syncwarp();
     u32 e1 = __shfl_down_sync(CST_FULL, e0, 1, G);
     u32 e2 = __shfl_down_sync(CST_FULL, e0, 2, G);
@@ -181,13 +182,13 @@ __device__ __forceinline__ bool canon_row(const T* __restrict__ row, int width, 
 
 // Term frequency of each lane's n-gram inside its own row via MATCH.ANY (restricted
 // to the row's lane group); the lowest lane of every set of equal keys is the leader
-// (the dict entry precook would create at that position).
-template <int G>
-__device__ __forceinline__ void row_tf(const u64 key[4], int lane, int only, int tf[4], bool lead[4]) {
-    const u32 gm = Grp<G>::mask(lane);
+// (the dict entry precook would create at that position).  `only` >= 0: this item
+// covers a single order (warp-uniform).
+__device__ __forceinline__ void row_tf(const u64 key[4], int lane, int G, int only, int tf[4], bool lead[4]) {
+    const u32 gm = grp_mask(lane, G);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (only >= 0 && k != only) {          // warp-uniform: this item covers a single order
+        if (only >= 0 && k != only) {
             tf[k] = 0;
             lead[k] = false;
             continue;
@@ -200,10 +201,9 @@ __device__ __forceinline__ void row_tf(const u64 key[4], int lane, int only, int
 
 // Sum four per-lane doubles over a lane group with a transposed butterfly (G = 32:
 // 6 exchanges instead of 20).  On return every lane holds the group total of ONE of
-// the four inputs: order o = group_order<G>(lane).
-template <int G>
-__device__ __forceinline__ double group_sum4_transposed(const double v[4], int lane) {
-    constexpr int HI = G / 2, MID = G / 4;
+// the four inputs: order o = group_order(lane, G).
+__device__ __forceinline__ double group_sum4_transposed(const double v[4], int lane, int G) {
+    const int HI = G >> 1, MID = G >> 2;
     const bool hi = (lane & HI) != 0;
     const bool mid = (lane & MID) != 0;
     // exchange with lane^HI: low half keeps orders {0,1}, high half keeps {2,3}
@@ -217,19 +217,17 @@ __device__ __forceinline__ double group_sum4_transposed(const double v[4], int l
     const double send = mid ? keepA : keepB;
     double x = mid ? keepB : keepA;
     x += __shfl_xor_sync(CST_FULL, send, MID);
-#pragma unroll
-    for (int o = MID / 2; o > 0; o >>= 1) x += __shfl_xor_sync(CST_FULL, x, o);
+#pragma unroll 1
+    for (int o = MID >> 1; o > 0; o >>= 1) x += __shfl_xor_sync(CST_FULL, x, o);
     return x;
 }
-template <int G>
-__device__ __forceinline__ int group_order(int lane) {
-    return ((lane & (G / 2)) ? 2 : 0) + ((lane & (G / 4)) ? 1 : 0);
+__device__ __forceinline__ int group_order(int lane, int G) {
+    return ((lane & (G >> 1)) ? 2 : 0) + ((lane & (G >> 2)) ? 1 : 0);
 }
-// sum of the four per-order values held by group_sum4_transposed's layout
-template <int G>
-__device__ __forceinline__ double group_sum_orders(double t) {
-    t += __shfl_xor_sync(CST_FULL, t, G / 2);
-    t += __shfl_xor_sync(CST_FULL, t, G / 4);
+// sum of the four per-order values held in group_sum4_transposed's layout
+__device__ __forceinline__ double group_sum_orders(double t, int G) {
+    t += __shfl_xor_sync(CST_FULL, t, G >> 1);
+    t += __shfl_xor_sync(CST_FULL, t, G >> 2);
     return t;
 }
 

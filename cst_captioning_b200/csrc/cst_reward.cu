@@ -301,8 +301,7 @@ extern "C" int cst_df_lookup(const cst_df_table* t, const uint64_t* keys, int64_
     return CST_OK;
 }
 
-template <typename T>
-__global__ void k_ngram_counts(const T* __restrict__ rows, int64_t n_rows, int width, int64_t stride,
+__global__ void k_ngram_counts(const void* __restrict__ rows, int is64, int64_t n_rows, int width, int64_t stride,
                                int use_eos, u64* keys_out, int* counts_out, int* n_out, int* len_out) {
     __shared__ u32 tokbuf[8][32];
     const int lane = threadIdx.x & 31;
@@ -311,23 +310,24 @@ __global__ void k_ngram_counts(const T* __restrict__ rows, int64_t n_rows, int w
     if (row >= n_rows) return;
     u64 key[4];
     int L;
-    canon_row<T, 32>(rows + row * stride, width, use_eos, lane, tokbuf[warp], key, L);
+    const char* base = reinterpret_cast<const char*>(rows) + (size_t)row * (size_t)stride * (is64 ? 8 : 4);
+    canon_row(base, is64, width, use_eos, lane, 32, tokbuf[warp], key, L);
     int tf[4];
     bool lead[4];
-    row_tf<32>(key, lane, -1, tf, lead);
-    int base = 0;
+    row_tf(key, lane, 32, -1, tf, lead);
+    int at0 = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         const u32 lm = __ballot_sync(CST_FULL, lead[k]);
         if (lead[k]) {
-            const int at = base + __popc(lm & lanemask_lt(lane));
+            const int at = at0 + __popc(lm & lanemask_lt(lane));
             keys_out[row * CST_NGRAM_SLOTS_PER_ROW + at] = key[k];
             counts_out[row * CST_NGRAM_SLOTS_PER_ROW + at] = tf[k];
         }
-        base += __popc(lm);
+        at0 += __popc(lm);
     }
     if (lane == 0) {
-        n_out[row] = base;
+        n_out[row] = at0;
         len_out[row] = L;
     }
 }
@@ -345,13 +345,8 @@ extern "C" int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows,
     DeviceGuard guard(device);
     if (!guard.ok) return fail(CST_E_CUDA, "cst_ngram_counts: cannot select device %d", device);
     const unsigned blocks = (unsigned)((n_rows + 7) / 8);
-    cudaStream_t st = (cudaStream_t)stream;
-    if (dtype == CST_DTYPE_I32)
-        k_ngram_counts<int32_t><<<blocks, 256, 0, st>>>((const int32_t*)rows, n_rows, width, stride, use_eos,
-                                                       (u64*)keys_out, counts_out, n_out, len_out);
-    else
-        k_ngram_counts<int64_t><<<blocks, 256, 0, st>>>((const int64_t*)rows, n_rows, width, stride, use_eos,
-                                                       (u64*)keys_out, counts_out, n_out, len_out);
+    k_ngram_counts<<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, dtype == CST_DTYPE_I64, n_rows, width, stride,
+                                                           use_eos, (u64*)keys_out, counts_out, n_out, len_out);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
@@ -463,10 +458,12 @@ struct ScoreParams {
     const double* gauss;
     const void* cand;
     const void* greedy;
+    int cand_is64;
     int64_t n_cand;
     int cand_width;
     int64_t cand_stride;
     const void* refs;
+    int ref_is64;
     int ref_width;
     int64_t ref_stride;
     const int64_t* ref_offsets;
@@ -492,131 +489,20 @@ struct ScoreParams {
 #define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
 #endif
 
-// Phase R for one reference row per lane group (G = 32: one row, G = 16: two rows of
-// this warp, one per half).  `width` = 0 marks an idle group (odd row count).  With
-// G = 16 a row whose canonical length exceeds 16 tokens yields no keys and is left to
-// the long-row pass.  `only` >= 0 restricts the item to one n-gram order (the long-row
-// pass spreads the four orders of a row over four warps), -1 = all four.
-// Returns the canonical length.
-template <typename RT, int G>
-__device__ __forceinline__ int ref_phase(const ScoreParams& p, const RT* row, int width, int rl, int lane, int only,
-                                         VidSlot* tab, double* invn, int* lenr, u32* tokbuf, bool& bad) {
-    u64 key[4];
-    int L;
-    bad = canon_row<RT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
-    const bool live = width > 0 && (G == 32 || L <= 16);
-    int tf[4];
-    bool lead[4];
-    row_tf<G>(key, lane, only, tf, lead);
-    u32 h[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
-    double idf[4];
-    df_probe4(p.df, key, h, lead, idf);
-
-    const u32 bit = 1u << rl;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        if (lead[k]) {
-            const u32 idx = vid_insert(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
-            atomicOr(&tab[idx].P, bit);
-            if (tf[k] > 1) {
-                atomicOr(&tab[idx].M, bit);
-                const u64 ck = count_key(idx, (u32)rl);
-                const u32 j = vid_insert(tab, p.tab_slots, vid_home(cst_hash(ck), p.tab_slots), ck);
-                tab[j].P = (u32)tf[k];
-            }
-        }
-    }
-    double n2[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
-        n2[k] = w * w;                                             // norm += vec ** 2
-    }
-    const double tot = group_sum4_transposed<G>(n2, lane);
-    if (live) {
-        const int o = group_order<G>(lane);
-        if ((lane & (G / 4 - 1)) == 0 && (only < 0 || o == only)) invn[o * 32 + rl] = inv_norm_of(tot);
-        if (Grp<G>::sl(lane) == 0 && only <= 0) lenr[rl] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
-    }
-    return L;
-}
-
-// Phase C for one candidate row per lane group: sum over the chunk's refs of
-// sum_n sim_n / (norm_h[n] norm_r[n]) * penalty  (not yet / n, / R, * 10), returned
-// in `score` on every lane of the group (restricted to order `only` if >= 0).
-template <typename CT, int G>
-__device__ __forceinline__ int cand_phase(const ScoreParams& p, const CT* row, int width, int nref, int lane, int only,
-                                          const VidSlot* tab, const double* invn, const int* lenr, double* gh,
-                                          u32* tokbuf, bool& bad, double& score) {
-    u64 key[4];
-    int L;
-    bad = canon_row<CT, G>(row, width, p.use_eos, lane, tokbuf, key, L);
-    int tf[4];
-    bool lead[4];
-    row_tf<G>(key, lane, only, tf, lead);
-    u32 h[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
-    double idf[4];
-    df_probe4(p.df, key, h, lead, idf);
-    double n2[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;
-        n2[k] = w * w;
-    }
-    const double invh = inv_norm_of(group_sum4_transposed<G>(n2, lane));
-
-    // Gaussian length penalty against every ref of the chunk (per-group buffer)
-    const int lenh = (L > 1) ? (L - 1) : 0;
-    double* g = gh + Grp<G>::sub(lane) * 32;
-    for (int r = Grp<G>::sl(lane); r < nref; r += G) g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
-    __syncwarp();
-
-    double num[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        double inner = 0.0;
-        if (lead[k]) {
-            const int idx = vid_find(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
-            if (idx >= 0) {
-                const u32 M = tab[idx].M;
-                u32 P = tab[idx].P & ~M;
-                const double* inv_k = invn + k * 32;
-                while (P) {                               // refs holding the n-gram once: min(tf_h, 1) * 1
-                    const int r = __ffs(P) - 1;
-                    P &= P - 1u;
-                    inner += inv_k[r] * g[r];
-                }
-                u32 Q = M;
-                while (Q) {                               // refs holding it more than once: exact count
-                    const int r = __ffs(Q) - 1;
-                    Q &= Q - 1u;
-                    const u64 ck = count_key((u32)idx, (u32)r);
-                    const int j = vid_find(tab, p.tab_slots, vid_home(cst_hash(ck), p.tab_slots), ck);
-                    const int c = (int)tab[j].P;
-                    const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
-                    inner += (double)m * (inv_k[r] * g[r]);
-                }
-            }
-        }
-        num[k] = idf[k] * idf[k] * inner;
-    }
-    score = group_sum_orders<G>(group_sum4_transposed<G>(num, lane) * invh);
-    __syncwarp();
-    return L;
-}
-
-template <typename CT, typename RT>
+// One CTA per video.  The body of the item loop exists ONCE in the code and serves
+//   phase 0 (R): the video's reference rows  -> per-video shared table, norms, lengths
+//   phase 1 (C): its candidate rows          -> scores
+// each in two passes: pass 0 handles two rows per warp (lane groups of 16), pass 1 the
+// rows longer than 16 tokens that pass 0 left aside, one row per warp -- or, when only
+// a few rows are long, one n-gram ORDER of a row per warp, so the extra pass is short
+// for the whole CTA.  Keeping a single copy matters: the kernel was instruction-fetch
+// bound when the four combinations were separate instantiations.
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // long rows met in phase R / phase C of the chunk
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
-    const int sub = lane >> 4;
     const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
 
     VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
@@ -635,10 +521,11 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
 
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
 #ifdef CST_PHASE_TIMING
-        long long tk0 = clock64(), tk1 = 0, tk2 = 0, tk3 = 0, tk4 = 0;
-#define CST_TICK(x) x = clock64()
+        long long tk[6];
+        tk[0] = clock64();
+#define CST_TICK(i) tk[i] = clock64()
 #else
-#define CST_TICK(x)
+#define CST_TICK(i)
 #endif
         int64_t r0, r1;
         if (p.ref_offsets) {
@@ -660,90 +547,168 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                 if (threadIdx.x < 2) s_nlong[threadIdx.x] = 0;
             }
             __syncthreads();
-            CST_TICK(tk1);
-            // ---- phase R: two reference rows per warp ----
-            const RT* ref0 = reinterpret_cast<const RT*>(p.refs) + c0 * p.ref_stride;
-            for (int base = 2 * warp; base < nref; base += 2 * nwarps) {
-                const int rl = base + sub;
-                const bool act = rl < nref;
-                bool bad;
-                const int L = ref_phase<RT, 16>(p, ref0 + (act ? rl : base) * p.ref_stride, act ? p.ref_width : 0, rl,
-                                                lane, -1, tab, invn, lenr, tokbuf, bad);
-                if (act && (lane & 15) == 0) {
-                    if (L > 16) long_r[atomicAdd(&s_nlong[0], 1)] = rl;      // left to the long-row pass
-                    else if (bad) ++bad_rows;
-                }
-            }
-            __syncthreads();
-            if (s_nlong[0] > 0) {
-                // long-row pass: one row per warp, or -- when few rows are long -- the four
-                // n-gram orders of a row on four warps, so the pass is short for everyone
-                const int nl = s_nlong[0];
-                const bool split = nl * 2 <= nwarps;
-                const int items = split ? nl * 4 : nl;
-                for (int it = warp; it < items; it += nwarps) {
-                    const int rl = long_r[split ? (it >> 2) : it];
-                    const int only = split ? (it & 3) : -1;
-                    bool bad;
-                    ref_phase<RT, 32>(p, ref0 + rl * p.ref_stride, p.ref_width, rl, lane, only, tab, invn, lenr,
-                                      tokbuf, bad);
-                    if (bad && lane == 0 && only <= 0) ++bad_rows;
-                }
-                __syncthreads();
-            }
-            CST_TICK(tk2);                               // the video table is complete
-            // ---- phase C: two candidate rows per warp ----
-            for (int base = 2 * warp; base < n_local; base += 2 * nwarps) {
-                const int c = base + sub;
-                const bool act = c < n_local;
-                const int cc = act ? c : base;
-                const bool is_greedy = cc >= p.cands_per_video;
-                const int64_t ci = video * p.cands_per_video + (is_greedy ? cc - p.cands_per_video : cc);
-                const CT* row = reinterpret_cast<const CT*>(is_greedy ? p.greedy : p.cand) + ci * p.cand_stride;
-                bool bad;
-                double t = 0.0;
-                const int L = cand_phase<CT, 16>(p, row, act ? p.cand_width : 0, nref, lane, -1, tab, invn, lenr, gh,
-                                                 tokbuf, bad, t);
-                if (act && (lane & 15) == 0) {
-                    if (L > 16) {
-                        long_c[atomicAdd(&s_nlong[1], 1)] = c;
-                    } else {
-                        sc[c] += t;
-                        if (bad && c0 == r0) ++bad_rows;
+            CST_TICK(1);
+
+#pragma unroll 1
+            for (int phase = 0; phase < 2; ++phase) {
+                const int n_items = phase ? n_local : nref;
+                int* long_list = phase ? long_c : long_r;
+#pragma unroll 1
+                for (int pass = 0; pass < 2; ++pass) {
+                    int G = 16, items = (n_items + 1) >> 1;
+                    bool split = false;
+                    if (pass == 1) {
+                        const int nl = s_nlong[phase];
+                        if (nl == 0) continue;                       // CTA-uniform
+                        G = 32;
+                        split = nl * 2 <= nwarps;
+                        items = split ? nl * 4 : nl;
                     }
-                }
-            }
-            __syncthreads();
-            if (s_nlong[1] > 0) {
-                const int nl = s_nlong[1];
-                const bool split = nl * 2 <= nwarps;
-                const int items = split ? nl * 4 : nl;
-                for (int it = warp; it < items; it += nwarps) {
-                    const int slot = split ? (it >> 2) : it;
-                    const int only = split ? (it & 3) : -1;
-                    const int cq = long_c[slot];
-                    const bool gq = cq >= p.cands_per_video;
-                    const int64_t cqi = video * p.cands_per_video + (gq ? cq - p.cands_per_video : cq);
-                    const CT* rq = reinterpret_cast<const CT*>(gq ? p.greedy : p.cand) + cqi * p.cand_stride;
-                    bool bad;
-                    double t = 0.0;
-                    cand_phase<CT, 32>(p, rq, p.cand_width, nref, lane, only, tab, invn, lenr, gh, tokbuf, bad, t);
-                    if (lane == 0) {
-                        if (split) {
-                            part[4 * slot + only] = t;
+#pragma unroll 1
+                    for (int it = warp; it < items; it += nwarps) {
+                        // ---- which row does this lane group work on? ----
+                        int ri, only = -1, slot = 0;
+                        bool act = true;
+                        if (pass == 0) {
+                            ri = 2 * it + (lane >> 4);
+                            act = ri < n_items;
+                            if (!act) ri = 2 * it;
                         } else {
-                            part[4 * slot] = t;
-                            part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
+                            slot = split ? (it >> 2) : it;
+                            only = split ? (it & 3) : -1;
+                            ri = long_list[slot];
                         }
-                        if (bad && c0 == r0 && only <= 0) ++bad_rows;
+                        const void* row;
+                        int is64, width;
+                        if (phase == 0) {
+                            is64 = p.ref_is64;
+                            width = p.ref_width;
+                            row = reinterpret_cast<const char*>(p.refs) +
+                                  (size_t)(c0 + ri) * (size_t)p.ref_stride * (is64 ? 8 : 4);
+                        } else {
+                            const bool gq = ri >= p.cands_per_video;
+                            const int64_t ci = video * p.cands_per_video + (gq ? ri - p.cands_per_video : ri);
+                            is64 = p.cand_is64;
+                            width = p.cand_width;
+                            row = reinterpret_cast<const char*>(gq ? p.greedy : p.cand) +
+                                  (size_t)ci * (size_t)p.cand_stride * (is64 ? 8 : 4);
+                        }
+                        if (!act) width = 0;                         // idle half of an odd pair
+
+                        // ---- front, common to references and candidates ----
+                        u64 key[4];
+                        int L;
+                        const bool bad = canon_row(row, is64, width, p.use_eos, lane, G, tokbuf, key, L);
+                        const int sl = grp_sl(lane, G);
+                        const bool live = act && L <= G;             // G = 16: longer rows wait for pass 1
+                        int tf[4];
+                        bool lead[4];
+                        row_tf(key, lane, G, only, tf, lead);
+                        u32 h[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
+                        double idf[4];
+                        df_probe4(p.df, key, h, lead, idf);
+                        double n2[4];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
+                            n2[k] = w * w;                                             // norm += vec ** 2
+                        }
+                        const double inv = inv_norm_of(group_sum4_transposed(n2, lane, G));   // own order's 1/norm
+                        const int o = group_order(lane, G);
+
+                        if (phase == 0) {
+                            // ---- phase R: publish the row into the video table ----
+                            const u32 bit = 1u << ri;
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                if (lead[k]) {
+                                    const u32 idx = vid_insert(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
+                                    atomicOr(&tab[idx].P, bit);
+                                    if (tf[k] > 1) {
+                                        atomicOr(&tab[idx].M, bit);
+                                        const u64 ck = count_key(idx, (u32)ri);
+                                        const u32 j = vid_insert(tab, p.tab_slots,
+                                                                 vid_home(cst_hash(ck), p.tab_slots), ck);
+                                        tab[j].P = (u32)tf[k];
+                                    }
+                                }
+                            }
+                            if (live) {
+                                if ((lane & ((G >> 2) - 1)) == 0 && (only < 0 || o == only)) invn[o * 32 + ri] = inv;
+                                if (sl == 0 && only <= 0) lenr[ri] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
+                            }
+                            if (act && sl == 0) {
+                                if (!live) long_list[atomicAdd(&s_nlong[0], 1)] = ri;
+                                else if (bad && only <= 0) ++bad_rows;
+                            }
+                        } else {
+                            // ---- phase C: score the row against the staged refs ----
+                            const int lenh = (L > 1) ? (L - 1) : 0;
+                            double* g = gh + (grp_shift(lane, G) & 16) * 2;
+                            for (int r = sl; r < nref; r += G)
+                                g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
+                            __syncwarp();
+                            double num[4];
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                double inner = 0.0;
+                                if (lead[k]) {
+                                    const int idx = vid_find(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
+                                    if (idx >= 0) {
+                                        const u32 M = tab[idx].M;
+                                        u32 P = tab[idx].P & ~M;
+                                        const double* inv_k = invn + k * 32;
+                                        while (P) {            // refs holding the n-gram once: min(tf_h, 1) * 1
+                                            const int r = __ffs(P) - 1;
+                                            P &= P - 1u;
+                                            inner += inv_k[r] * g[r];
+                                        }
+                                        u32 Q = M;
+                                        while (Q) {            // refs holding it more than once: exact count
+                                            const int r = __ffs(Q) - 1;
+                                            Q &= Q - 1u;
+                                            const u64 ck = count_key((u32)idx, (u32)r);
+                                            const int j = vid_find(tab, p.tab_slots,
+                                                                   vid_home(cst_hash(ck), p.tab_slots), ck);
+                                            const int c = (int)tab[j].P;
+                                            const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
+                                            inner += (double)m * (inv_k[r] * g[r]);
+                                        }
+                                    }
+                                }
+                                num[k] = idf[k] * idf[k] * inner;
+                            }
+                            const double t = group_sum_orders(group_sum4_transposed(num, lane, G) * inv, G);
+                            __syncwarp();
+                            if (act && sl == 0) {
+                                if (!live) {
+                                    long_list[atomicAdd(&s_nlong[1], 1)] = ri;
+                                } else {
+                                    if (pass == 0) {
+                                        sc[ri] += t;
+                                    } else if (split) {
+                                        part[4 * slot + only] = t;
+                                    } else {
+                                        part[4 * slot] = t;
+                                        part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
+                                    }
+                                    if (bad && c0 == r0 && only <= 0) ++bad_rows;
+                                }
+                            }
+                        }
+                    }
+                    __syncthreads();
+                    if (phase == 1 && pass == 1) {
+                        const int nl = s_nlong[1];
+                        for (int i = threadIdx.x; i < nl; i += blockDim.x)       // fixed order: deterministic
+                            sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
+                        __syncthreads();                 // all probes done before the table is cleared again
                     }
                 }
-                __syncthreads();
-                for (int i = threadIdx.x; i < nl; i += blockDim.x)       // fixed order: deterministic
-                    sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
-                __syncthreads();                         // all probes done before the table is cleared again
+                CST_TICK(2 + phase);
             }
-            CST_TICK(tk3);
         }
         if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
         if (bad_rows && p.ctl) atomicAdd(&p.ctl[1], bad_rows);
@@ -809,13 +774,13 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
         }
         __syncthreads();
 #ifdef CST_PHASE_TIMING
-        CST_TICK(tk4);
-        if (p.ctl && (threadIdx.x & 31) == 0) {      // per warp: where its time went (cycles)
+        CST_TICK(4);
+        if (p.ctl && (threadIdx.x & 31) == 0) {      // per warp: where its time went (cycles, last chunk)
             unsigned long long* t = reinterpret_cast<unsigned long long*>(p.ctl) + 8;
-            atomicAdd(t + 0, (unsigned long long)(tk1 - tk0));
-            atomicAdd(t + 1, (unsigned long long)(tk2 - tk1));
-            atomicAdd(t + 2, (unsigned long long)(tk3 - tk2));
-            atomicAdd(t + 3, (unsigned long long)(tk4 - tk3));
+            atomicAdd(t + 0, (unsigned long long)(tk[1] - tk[0]));
+            atomicAdd(t + 1, (unsigned long long)(tk[2] - tk[1]));
+            atomicAdd(t + 2, (unsigned long long)(tk[3] - tk[2]));
+            atomicAdd(t + 3, (unsigned long long)(tk[4] - tk[3]));
             atomicAdd(t + 4, 1ull);
         }
 #endif
@@ -871,17 +836,16 @@ static void stat_counts(int mode, int64_t n_cand, int seq_per_img, int k, double
     }
 }
 
-template <typename CT, typename RT>
 static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st) {
     static thread_local size_t configured[64] = {0};
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || configured[dev] < smem) {
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CT, RT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = smem;
     }
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
-    k_score<CT, RT><<<grid, threads, smem, st>>>(p);
+    k_score<<<grid, threads, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
@@ -924,6 +888,8 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     p.gauss = t->gauss;
     p.cand = cand;
     p.greedy = greedy;
+    p.cand_is64 = (cand_dtype == CST_DTYPE_I64);
+    p.ref_is64 = (ref_dtype == CST_DTYPE_I64);
     p.n_cand = n_cand;
     p.cand_width = cand_width;
     p.cand_stride = cand_stride;
@@ -969,10 +935,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 
     const int threads = nwarps * 32;
-    if (cand_dtype == CST_DTYPE_I32 && ref_dtype == CST_DTYPE_I32) return launch_score<int32_t, int32_t>(p, threads, smem, st);
-    if (cand_dtype == CST_DTYPE_I64 && ref_dtype == CST_DTYPE_I64) return launch_score<int64_t, int64_t>(p, threads, smem, st);
-    if (cand_dtype == CST_DTYPE_I64 && ref_dtype == CST_DTYPE_I32) return launch_score<int64_t, int32_t>(p, threads, smem, st);
-    return launch_score<int32_t, int64_t>(p, threads, smem, st);
+    return launch_score(p, threads, smem, st);
 }
 
 extern "C" int cst_cider_scores(const cst_df_table* table, const void* cand, const void* greedy,
@@ -1071,8 +1034,7 @@ __device__ __forceinline__ bool set_insert_new(u64* keys, u32 mask, u32 idx, u64
 
 // One CTA per video: the set union of its refs' n-grams is formed in shared memory
 // (compute_ciderdf.py:66-67); each member then adds 1 to its global counter (:68).
-template <typename T>
-__global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, int width, int64_t stride,
+__global__ void __launch_bounds__(256) k_df_build(const void* __restrict__ rows, int is64, int width, int64_t stride,
                                                   int use_eos, const int64_t* __restrict__ video_offsets,
                                                   int64_t n_videos, u32 set_slots, int set_shift, u64* g_keys,
                                                   u32* g_cnt, u32 g_cap, u32* n_unique, u32* n_bad) {
@@ -1088,11 +1050,12 @@ __global__ void __launch_bounds__(256) k_df_build(const T* __restrict__ rows, in
         for (int64_t r = r0 + warp; r < r1; r += nwarps) {
             u64 key[4];
             int L;
-            const bool bad = canon_row<T, 32>(rows + r * stride, width, use_eos, lane, tokbuf, key, L);
+            const char* row = reinterpret_cast<const char*>(rows) + (size_t)r * (size_t)stride * (is64 ? 8 : 4);
+            const bool bad = canon_row(row, is64, width, use_eos, lane, 32, tokbuf, key, L);
             if (bad && lane == 0) atomicAdd(n_bad, 1u);
             int tf[4];
             bool lead[4];
-            row_tf<32>(key, lane, -1, tf, lead);
+            row_tf(key, lane, 32, -1, tf, lead);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 if (!lead[k]) continue;
@@ -1203,17 +1166,9 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     BUILD_TRY(cudaMemset(g_cnt, 0, (size_t)g_cap * sizeof(u32)));
     BUILD_TRY(cudaMemset(counters, 0, 2 * sizeof(u32)));
     BUILD_TRY(cudaMemcpy(d_off, video_offsets, (size_t)(n_videos + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
-    if (dtype == CST_DTYPE_I32) {
-        BUILD_TRY(cudaFuncSetAttribute(k_df_build<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_df_build<int32_t><<<grid, 256, smem>>>((const int32_t*)rows, width, stride, use_eos ? 1 : 0, d_off,
-                                                 n_videos, set_slots, set_shift, g_keys, g_cnt, g_cap, counters,
-                                                 counters + 1);
-    } else {
-        BUILD_TRY(cudaFuncSetAttribute(k_df_build<int64_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_df_build<int64_t><<<grid, 256, smem>>>((const int64_t*)rows, width, stride, use_eos ? 1 : 0, d_off,
-                                                 n_videos, set_slots, set_shift, g_keys, g_cnt, g_cap, counters,
-                                                 counters + 1);
-    }
+    BUILD_TRY(cudaFuncSetAttribute(k_df_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_df_build<<<grid, 256, smem>>>(rows, dtype == CST_DTYPE_I64, width, stride, use_eos ? 1 : 0, d_off, n_videos,
+                                    set_slots, set_shift, g_keys, g_cnt, g_cap, counters, counters + 1);
     COUNT_LAUNCH();
     BUILD_TRY(cudaGetLastError());
     BUILD_TRY(cudaMemcpy(h_counters, counters, sizeof(h_counters), cudaMemcpyDeviceToHost));
