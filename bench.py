@@ -292,7 +292,7 @@ def product_arm(args):
     achieved = n_cap * BYTES_PER_CAPTION / (kern_ms * 1e-3) / 1e9
     traffic = ncu_traffic()
     roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                'traffic': traffic['bytes_per_launch'] if traffic else None, 'kernel': 'k_score<int,int>',
+                'traffic': traffic['bytes_per_launch'] if traffic else None, 'kernel': 'k_score',
                 'kernel_ms': kern_ms, 'bytes_per_caption': BYTES_PER_CAPTION, 'peak_source': peak_src,
                 'frac_of_nominal_8TBs': achieved / 8000.0}
 
