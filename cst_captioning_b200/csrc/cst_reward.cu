@@ -614,6 +614,10 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                         for (int k = 0; k < 4; ++k) {
                             const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
                             n2[k] = w * w;                                             // norm += vec ** 2
+                            // an n-gram every document holds (<end>, the commonest words) has idf = 0:
+                            // its tf-idf entries are exact zeros on both sides, so it needs no table entry
+                            // and no probe -- and it is the one n-gram that sits in ALL refs of a video
+                            lead[k] = lead[k] && idf[k] != 0.0;
                         }
                         const double inv = inv_norm_of(group_sum4_transposed(n2, lane, G));   // own order's 1/norm
                         const int o = group_order(lane, G);
