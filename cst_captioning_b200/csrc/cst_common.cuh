@@ -21,7 +21,9 @@ typedef unsigned int u32;
 //   keys     [n_buckets][4] u64   open addressing over 32-byte buckets: one
 //                                 256-bit load (one L2 sector) fetches a whole
 //                                 bucket; a bucket with an empty slot ends a probe
-//   dfc      [n_buckets][4] u32   document frequency of the key in the same slot
+//   idfv     [n_buckets][4] f64   idf of the key in the same slot = lut[df]: ONE dependent
+//                                 load after the bucket (df -> lut would be two L2 trips)
+//   dfc      [n_buckets][4] u32   its document frequency (cold: parity probe, export)
 //   lut      [n_documents + 1]    idf by document frequency, float64 computed by the
 //                                 caller (bit-identical to the scorer's numpy value)
 //   uni      [CST_UNI_N] f64      idf of unigram `token` directly (no hashing)
@@ -31,6 +33,7 @@ typedef unsigned int u32;
 
 struct DfView {
     const u64* keys;
+    const double* idfv;
     const u32* dfc;
     const double* lut;
     const double* uni;
@@ -72,7 +75,7 @@ __device__ __forceinline__ int bucket_resolve(const u64* __restrict__ keys, u32 
 
 // idf of the four n-grams of a lane.  Order 1 is a direct load; the bucket loads of
 // orders 2..4 are issued back to back so their L2 round trips overlap, then the
-// df loads, then the (L1-resident) idf LUT loads.
+// idf loads of the slots that matched.
 __device__ __forceinline__ void df_probe4(const DfView& t, const u64 key[4], const u32 h[4], const bool need[4],
                                           double idf[4]) {
     const u32 tok = (u32)key[0] - 1u;
@@ -88,12 +91,9 @@ __device__ __forceinline__ void df_probe4(const DfView& t, const u64 key[4], con
     int slot[4];
 #pragma unroll
     for (int k = 1; k < 4; ++k) slot[k] = need[k] ? bucket_resolve(t.keys, t.n_buckets, b[k], kk[k], key[k]) : -1;
-    u32 d[4];
-#pragma unroll
-    for (int k = 1; k < 4; ++k) d[k] = (slot[k] >= 0) ? __ldg(t.dfc + slot[k]) : 0u;
     idf[0] = w0;
 #pragma unroll
-    for (int k = 1; k < 4; ++k) idf[k] = (slot[k] >= 0) ? __ldg(t.lut + d[k]) : t.unseen;
+    for (int k = 1; k < 4; ++k) idf[k] = (slot[k] >= 0) ? __ldg(t.idfv + slot[k]) : t.unseen;
 }
 
 __device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u; }

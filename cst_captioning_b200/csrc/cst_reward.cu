@@ -64,6 +64,7 @@ struct cst_df_table {
     int64_t n_documents;
     double idf_unseen;
     u64* keys;       // [n_buckets * 4]
+    double* idfv;    // [n_buckets * 4]
     u32* dfc;        // [n_buckets * 4]
     double* lut;     // [n_documents + 1]
     double* uni;     // [CST_UNI_N]
@@ -73,6 +74,7 @@ struct cst_df_table {
 static DfView view_of(const cst_df_table* t) {
     DfView v;
     v.keys = t->keys;
+    v.idfv = t->idfv;
     v.dfc = t->dfc;
     v.lut = t->lut;
     v.uni = t->uni;
@@ -112,6 +114,7 @@ static int table_alloc(int device, u32 n_buckets, const double* idf_by_df, int64
     const size_t slots = (size_t)n_buckets * CST_BUCKET;
     cudaError_t e = cudaMalloc(&t->keys, slots * sizeof(u64));
     if (e == cudaSuccess) e = cudaMalloc(&t->dfc, slots * sizeof(u32));
+    if (e == cudaSuccess) e = cudaMalloc(&t->idfv, slots * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&t->lut, (size_t)(n_documents + 1) * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&t->uni, (size_t)CST_UNI_N * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&t->gauss, sizeof(g));
@@ -122,6 +125,7 @@ static int table_alloc(int device, u32 n_buckets, const double* idf_by_df, int64
     if (e != cudaSuccess) {
         cudaFree(t->keys);
         cudaFree(t->dfc);
+        cudaFree(t->idfv);
         cudaFree(t->lut);
         cudaFree(t->uni);
         cudaFree(t->gauss);
@@ -131,6 +135,14 @@ static int table_alloc(int device, u32 n_buckets, const double* idf_by_df, int64
     }
     *out = t;
     return CST_OK;
+}
+
+// idfv[slot] = lut[dfc[slot]] for every stored key
+__global__ void k_fill_idf(const u64* __restrict__ keys, const u32* __restrict__ dfc, const double* __restrict__ lut,
+                           double* idfv, size_t slots) {
+    const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= slots) return;
+    idfv[s] = keys[s] ? lut[dfc[s]] : 0.0;
 }
 
 // uni[token] = idf of the unigram `token` (direct-indexed shortcut of the hash table)
@@ -146,6 +158,10 @@ __global__ void k_fill_uni(DfView t, double* uni) {
 }
 
 static int table_finish(cst_df_table* t) {
+    const size_t slots = (size_t)t->n_buckets * CST_BUCKET;
+    k_fill_idf<<<(unsigned)((slots + 255) / 256), 256>>>(t->keys, t->dfc, t->lut, t->idfv, slots);
+    COUNT_LAUNCH();
+    CUDA_TRY(cudaGetLastError());
     k_fill_uni<<<(CST_UNI_N + 255) / 256, 256>>>(view_of(t), t->uni);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
@@ -229,6 +245,7 @@ extern "C" int cst_df_destroy(cst_df_table* t) {
     DeviceGuard guard(t->device);
     cudaFree(t->keys);
     cudaFree(t->dfc);
+    cudaFree(t->idfv);
     cudaFree(t->lut);
     cudaFree(t->uni);
     cudaFree(t->gauss);
@@ -279,7 +296,7 @@ __global__ void k_df_lookup(DfView t, const u64* __restrict__ keys, int64_t n, d
         if (slot >= 0) {
             const u32 c = t.dfc[slot];
             d = (double)c;
-            w = t.lut[c];
+            w = t.idfv[slot];
         }
         if ((key >> 16) == 0ull && (u32)key - 1u < CST_UNI_N) w = t.uni[(u32)key - 1u];
     }
@@ -500,6 +517,7 @@ struct ScoreParams {
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // long rows met in phase R / phase C of the chunk
+    __shared__ double s_gauss[CST_GAUSS_N];          // length-penalty LUT (a global load here would be an L2 trip)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
@@ -518,6 +536,9 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
     u32* tok_all = reinterpret_cast<u32*>(long_c + n_local);        // [nwarps][32]
     double* gh = gh_all + warp * 64;
     u32* tokbuf = tok_all + warp * 32;
+
+    for (int i = threadIdx.x; i < CST_GAUSS_N; i += blockDim.x) s_gauss[i] = p.gauss[i];
+    // (visible to the CTA after the __syncthreads that follows the first table clear)
 
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
 #ifdef CST_PHASE_TIMING
@@ -652,7 +673,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                             const int lenh = (L > 1) ? (L - 1) : 0;
                             double* g = gh + (grp_shift(lane, G) & 16) * 2;
                             for (int r = sl; r < nref; r += G)
-                                g[r] = __ldg(p.gauss + (lenh - lenr[r] + CST_GAUSS_HALF));
+                                g[r] = s_gauss[lenh - lenr[r] + CST_GAUSS_HALF];
                             __syncwarp();
                             double num[4];
 #pragma unroll
