@@ -134,6 +134,25 @@ __device__ __forceinline__ long long ld_tok(const void* row, int is64, int i) {
                 : (long long)__ldcs(reinterpret_cast<const int*>(row) + i);
 }
 
+// Canonical token count of a row only (the pre-scan that finds the rows too long for a
+// 16-lane group); same rules as canon_row.
+__device__ __forceinline__ int canon_len(const void* row, int is64, int width, int use_eos, int lane, int G) {
+    const int sl = grp_sl(lane, G);
+    const bool half = (G == 16);
+    const int pa = sl, pb = sl + 16;
+    const bool ina = pa < width;
+    const bool inb = half && pb < width;
+    const long long ta = ina ? ld_tok(row, is64, pa) : 0ll;
+    const long long tb = inb ? ld_tok(row, is64, pb) : 0ll;
+    const bool bada = ina && (ta < -1 || ta > 65534);
+    const bool badb = inb && (tb < -1 || tb > 65534);
+    const u32 tmask = grp_vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane, G);
+    const int end = tmask ? (__ffs(tmask) - 1) : width;
+    const bool keepa = (pa < end && ta != 1) || (use_eos && pa == end && ina && ta == 0);
+    const bool keepb = half && ((pb < end && tb != 1) || (use_eos && pb == end && inb && tb == 0));
+    return __popc(grp_vote(keepa, keepb, lane, G));
+}
+
 __device__ __forceinline__ bool canon_row(const void* row, int is64, int width, int use_eos, int lane, int G,
                                           u32* tokbuf, u64 key[4], int& L) {
     const int sl = grp_sl(lane, G);

@@ -516,7 +516,9 @@ struct ScoreParams {
 // bound when the four combinations were separate instantiations.
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int s_nlong[2];                       // long rows met in phase R / phase C of the chunk
+    __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
+    __shared__ int s_ticket[2];                      // next item of the phase's work list
+    __shared__ int s_started[2];                     // pair items past their canonicalisation
     __shared__ double s_gauss[CST_GAUSS_N];          // length-penalty LUT (a global load here would be an L2 trip)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -562,43 +564,61 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
 
         for (int64_t c0 = r0; c0 < r1; c0 += p.chunk_refs) {
             const int nref = (int)((r1 - c0) < (int64_t)p.chunk_refs ? (r1 - c0) : (int64_t)p.chunk_refs);
-            {   // clear the video table
+            {   // clear the video table and the work-list counters
                 uint4* z = reinterpret_cast<uint4*>(tab);
                 for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
-                if (threadIdx.x < 2) s_nlong[threadIdx.x] = 0;
+                if (threadIdx.x < 2) {
+                    s_nlong[threadIdx.x] = 0;
+                    s_ticket[threadIdx.x] = 0;
+                    s_started[threadIdx.x] = 0;
+                }
             }
             __syncthreads();
             CST_TICK(1);
 
 #pragma unroll 1
             for (int phase = 0; phase < 2; ++phase) {
+                // One dynamic work list per phase: first the row pairs (two rows per warp, lane groups
+                // of 16), then the rows the pairs found too long for 16 lanes -- a long row is one item
+                // or, when few rows are long, four items (one n-gram order each).  Warps draw tickets,
+                // so whoever finishes a pair early takes a long-row item instead of idling at a barrier.
+                // The list of long rows is complete once every pair item is past its canonicalisation
+                // (s_started == n_pairs); a warp that wants a long-row item waits for that, which is
+                // brief and cannot deadlock: pair tickets are all drawn before any long-row ticket, and
+                // a pair item reaches that point without waiting on anybody.
                 const int n_items = phase ? n_local : nref;
                 int* long_list = phase ? long_c : long_r;
+                const int n_pairs = (n_items + 1) >> 1;
+                int nl = 0;
+                bool split = false;
 #pragma unroll 1
-                for (int pass = 0; pass < 2; ++pass) {
-                    int G = 16, items = (n_items + 1) >> 1;
-                    bool split = false;
-                    if (pass == 1) {
-                        const int nl = s_nlong[phase];
-                        if (nl == 0) continue;                       // CTA-uniform
-                        G = 32;
-                        split = nl * 2 <= nwarps;
-                        items = split ? nl * 4 : nl;
-                    }
-#pragma unroll 1
-                    for (int it = warp; it < items; it += nwarps) {
-                        // ---- which row does this lane group work on? ----
-                        int ri, only = -1, slot = 0;
-                        bool act = true;
-                        if (pass == 0) {
-                            ri = 2 * it + (lane >> 4);
-                            act = ri < n_items;
-                            if (!act) ri = 2 * it;
-                        } else {
-                            slot = split ? (it >> 2) : it;
-                            only = split ? (it & 3) : -1;
-                            ri = long_list[slot];
+                for (;;) {
+                    int q = 0;
+                    if (lane == 0) q = atomicAdd(&s_ticket[phase], 1);
+                    q = __shfl_sync(CST_FULL, q, 0);
+                    // ---- which row does this lane group work on? ----
+                    int G, ri, only = -1, slot = 0;
+                    bool act = true;
+                    if (q < n_pairs) {
+                        G = 16;
+                        ri = 2 * q + (lane >> 4);
+                        act = ri < n_items;
+                        if (!act) ri = 2 * q;
+                    } else {
+                        if (lane == 0) {
+                            while (*reinterpret_cast<volatile int*>(&s_started[phase]) < n_pairs) { }
                         }
+                        __syncwarp();
+                        nl = *reinterpret_cast<volatile int*>(&s_nlong[phase]);
+                        split = nl * 2 <= nwarps;
+                        if (q >= n_pairs + (split ? nl * 4 : nl)) break;
+                        G = 32;
+                        const int j = q - n_pairs;
+                        slot = split ? (j >> 2) : j;
+                        only = split ? (j & 3) : -1;
+                        ri = *reinterpret_cast<volatile int*>(&long_list[slot]);
+                    }
+                    {
                         const void* row;
                         int is64, width;
                         if (phase == 0) {
@@ -621,7 +641,15 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                         int L;
                         const bool bad = canon_row(row, is64, width, p.use_eos, lane, G, tokbuf, key, L);
                         const int sl = grp_sl(lane, G);
-                        const bool live = act && L <= G;             // G = 16: longer rows wait for pass 1
+                        const bool live = act && L <= G;             // G = 16: longer rows become items of their own
+                        if (G == 16) {
+                            if (act && !live && sl == 0) long_list[atomicAdd(&s_nlong[phase], 1)] = ri;
+                            __syncwarp();
+                            if (lane == 0) {
+                                __threadfence_block();               // the list entries before the count
+                                atomicAdd(&s_started[phase], 1);
+                            }
+                        }
                         int tf[4];
                         bool lead[4];
                         row_tf(key, lane, G, only, tf, lead);
@@ -664,10 +692,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                                 if ((lane & ((G >> 2) - 1)) == 0 && (only < 0 || o == only)) invn[o * 32 + ri] = inv;
                                 if (sl == 0 && only <= 0) lenr[ri] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
                             }
-                            if (act && sl == 0) {
-                                if (!live) long_list[atomicAdd(&s_nlong[0], 1)] = ri;
-                                else if (bad && only <= 0) ++bad_rows;
-                            }
+                            if (live && sl == 0 && bad && only <= 0) ++bad_rows;
                         } else {
                             // ---- phase C: score the row against the staged refs ----
                             const int lenh = (L > 1) ? (L - 1) : 0;
@@ -707,30 +732,26 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                             }
                             const double t = group_sum_orders(group_sum4_transposed(num, lane, G) * inv, G);
                             __syncwarp();
-                            if (act && sl == 0) {
-                                if (!live) {
-                                    long_list[atomicAdd(&s_nlong[1], 1)] = ri;
+                            if (live && sl == 0) {
+                                if (G == 16) {
+                                    sc[ri] += t;
+                                } else if (split) {
+                                    part[4 * slot + only] = t;
                                 } else {
-                                    if (pass == 0) {
-                                        sc[ri] += t;
-                                    } else if (split) {
-                                        part[4 * slot + only] = t;
-                                    } else {
-                                        part[4 * slot] = t;
-                                        part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
-                                    }
-                                    if (bad && c0 == r0 && only <= 0) ++bad_rows;
+                                    part[4 * slot] = t;
+                                    part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
                                 }
+                                if (bad && c0 == r0 && only <= 0) ++bad_rows;
                             }
                         }
                     }
-                    __syncthreads();
-                    if (phase == 1 && pass == 1) {
-                        const int nl = s_nlong[1];
-                        for (int i = threadIdx.x; i < nl; i += blockDim.x)       // fixed order: deterministic
-                            sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
-                        __syncthreads();                 // all probes done before the table is cleared again
-                    }
+                }
+                __syncthreads();
+                nl = s_nlong[phase];
+                if (phase == 1 && nl > 0) {
+                    for (int i = threadIdx.x; i < nl; i += blockDim.x)           // fixed order: deterministic
+                        sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
+                    __syncthreads();                     // all probes done before the table is cleared again
                 }
                 CST_TICK(2 + phase);
             }
