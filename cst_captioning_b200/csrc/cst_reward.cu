@@ -519,6 +519,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
     __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
     __shared__ int s_ticket[2];                      // next item of the phase's work list
     __shared__ int s_started[2];                     // pair items past their canonicalisation
+    __shared__ int s_done_r;                         // reference items fully published
     __shared__ double s_gauss[CST_GAUSS_N];          // length-penalty LUT (a global load here would be an L2 trip)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -572,9 +573,11 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                     s_ticket[threadIdx.x] = 0;
                     s_started[threadIdx.x] = 0;
                 }
+                if (threadIdx.x == 2) s_done_r = 0;
             }
             __syncthreads();
             CST_TICK(1);
+            bool refs_ready = false;                     // warp-uniform
 
 #pragma unroll 1
             for (int phase = 0; phase < 2; ++phase) {
@@ -693,8 +696,28 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                                 if (sl == 0 && only <= 0) lenr[ri] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
                             }
                             if (live && sl == 0 && bad && only <= 0) ++bad_rows;
+                            __syncwarp();
+                            if (lane == 0) {
+                                __threadfence_block();               // this item's table entries before the count
+                                atomicAdd(&s_done_r, 1);
+                            }
                         } else {
                             // ---- phase C: score the row against the staged refs ----
+                            // There is no CTA barrier between the phases: a warp that ran out of reference
+                            // items has already done the table-independent half of this candidate item
+                            // above; here it waits until every reference item has been published.  Reference
+                            // items never wait on candidate items, so this cannot deadlock.
+                            if (!refs_ready) {
+                                if (lane == 0) {
+                                    const int np_r = (nref + 1) >> 1;
+                                    while (*reinterpret_cast<volatile int*>(&s_started[0]) < np_r) { }
+                                    const int nlr = *reinterpret_cast<volatile int*>(&s_nlong[0]);
+                                    const int total_r = np_r + ((nlr * 2 <= nwarps) ? nlr * 4 : nlr);
+                                    while (*reinterpret_cast<volatile int*>(&s_done_r) < total_r) { }
+                                }
+                                __syncwarp();
+                                refs_ready = true;
+                            }
                             const int lenh = (L > 1) ? (L - 1) : 0;
                             double* g = gh + (grp_shift(lane, G) & 16) * 2;
                             for (int r = sl; r < nref; r += G)
@@ -745,6 +768,10 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                             }
                         }
                     }
+                }
+                if (phase == 0) {                         // no barrier here: see the wait in phase C
+                    CST_TICK(2);
+                    continue;
                 }
                 __syncthreads();
                 nl = s_nlong[phase];
