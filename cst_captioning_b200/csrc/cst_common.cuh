@@ -199,22 +199,30 @@ __device__ __forceinline__ bool canon_row(const void* row, int is64, int width, 
     return (bmask & upto_end) != 0u;
 }
 
-// Term frequency of each lane's n-gram inside its own row via MATCH.ANY (restricted
-// to the row's lane group); the lowest lane of every set of equal keys is the leader
-// (the dict entry precook would create at that position).  `only` >= 0: this item
-// covers a single order (warp-uniform).
+// Term frequency of each lane's n-gram inside its own row; the lowest lane of every set
+// of equal n-grams is the leader (the dict entry precook would create at that position).
+// One MATCH.ANY on the unigrams gives E1(i) = positions holding the same token as i; the
+// higher orders follow from it without further matching:
+//     E_k(i) = E_{k-1}(i) & (E_1(i + k - 1) >> (k - 1))
+// (positions j whose tokens j .. j+k-1 equal tokens i .. i+k-1).  Positions past the
+// end hold token code 0, which never equals a real token code, so partial n-grams drop
+// out by themselves.  `only` >= 0: this item covers a single order (warp-uniform).
 __device__ __forceinline__ void row_tf(const u64 key[4], int lane, int G, int only, int tf[4], bool lead[4]) {
-    const u32 gm = grp_mask(lane, G);
+    const int sh = grp_shift(lane, G);
+    const int sl = grp_sl(lane, G);
+    const u32 window = (G == 32) ? CST_FULL : 0xffffu;
+    const u32 e1 = (__match_any_sync(CST_FULL, (u32)key[0]) >> sh) & window;   // group-relative positions
+    u32 ek = e1;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (only >= 0 && k != only) {
-            tf[k] = 0;
-            lead[k] = false;
-            continue;
+        if (k > 0) {
+            u32 nb = __shfl_down_sync(CST_FULL, e1, k, G);        // E1 of position sl + k
+            if (sl + k >= G) nb = 0u;
+            ek &= nb >> k;
         }
-        const u32 m = __match_any_sync(CST_FULL, key[k]) & gm;
-        tf[k] = __popc(m);
-        lead[k] = (key[k] != 0ull) && ((__ffs(m) - 1) == lane);
+        const bool mine = (only < 0 || k == only);
+        tf[k] = mine ? __popc(ek) : 0;
+        lead[k] = mine && (key[k] != 0ull) && ((__ffs(ek) - 1) == sl);
     }
 }
 
