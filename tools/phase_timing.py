@@ -25,6 +25,8 @@ cst.get_cst_reward(c, r, scorer, **kw)
 torch.cuda.synchronize()
 t1 = scratch[64:64 + 40].clone().view(torch.int64).cpu().numpy()
 d = (t1 - t0).astype(np.float64)
+if d[4] == 0:
+    raise SystemExit('no counters: rebuild with CST_NVCC_EXTRA=-DCST_PHASE_TIMING python __graft_entry__.py --force')
 names = ['clear+wait', 'phase R (+barrier)', 'phase C (+barrier)', 'phase B']
 for nm, v in zip(names, d[:4] / d[4]):
     print('%-22s %10.0f cycles per warp per video' % (nm, v))
