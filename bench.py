@@ -329,6 +329,24 @@ def product_arm(args):
            'api': 'HostRewardPipeline (pinned host rows, %d slices, upload overlapped with scoring)' % args.e2e_slices,
            'ms_per_step': 1e3 * e2e_s / e2e_steps}
 
+    # informational: the same pipeline fed int16 host rows (ids <= 32767 fit; half the upload)
+    h_cand16, h_refs16 = h_cand.to(torch.int16).pin_memory(), h_refs.to(torch.int16).pin_memory()
+
+    def e2e16_step():
+        _, st = pipe(h_cand16, h_refs16, out=out_pin)
+        st_pin.copy_(st, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e16_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e16_step()
+    barrier()
+    e2e16_s = time.perf_counter() - t0
+    e2e['int16_host_rows'] = {'value': n_cap * e2e_steps / e2e16_s, 'unit': UNIT + ' per GPU', 'ms_per_step': 1e3 * e2e16_s / e2e_steps,
+                              'h2d_bytes_per_step': int(h_cand16.numel() * 2 + h_refs16.numel() * 2)}
+
     # ---- CPU baseline: oracle port, one core, bounded sample (rank 0, N = 1 only) --
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get('CST_REWARD_LIB') or os.path.join(_HERE, 'libcst_reward.so')
 
 OK, E_ARG, E_CUDA, E_NOMEM, E_RANGE = 0, -1, -2, -3, -4
-DTYPE_I32, DTYPE_I64 = 0, 1
+DTYPE_I32, DTYPE_I64, DTYPE_I16 = 0, 1, 2
 BASE_NONE, BASE_GREEDY, BASE_SCB_GT, BASE_SCB_SAMPLE = 0, 1, 2, 3
 MAX_ROW_WIDTH = 32
 MAX_TOKEN_ID = 65534

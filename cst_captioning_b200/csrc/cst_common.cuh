@@ -128,22 +128,24 @@ __device__ __forceinline__ u32 grp_vote(bool pa, bool pb, int lane, int G) {
     return (G == 32) ? a : (((a >> sh) & 0xffffu) | (((b >> sh) & 0xffffu) << 16));
 }
 
-// token `i` of a row of int32 or int64 ids; rows stream through once: evict-first
-__device__ __forceinline__ long long ld_tok(const void* row, int is64, int i) {
-    return is64 ? (long long)__ldcs(reinterpret_cast<const long long*>(row) + i)
-                : (long long)__ldcs(reinterpret_cast<const int*>(row) + i);
+// token `i` of a row of int16, int32 or int64 ids (`esz` = bytes per id); rows stream
+// through once: evict-first
+__device__ __forceinline__ long long ld_tok(const void* row, int esz, int i) {
+    if (esz == 4) return (long long)__ldcs(reinterpret_cast<const int*>(row) + i);
+    if (esz == 8) return (long long)__ldcs(reinterpret_cast<const long long*>(row) + i);
+    return (long long)__ldcs(reinterpret_cast<const short*>(row) + i);
 }
 
 // Canonical token count of a row only (the pre-scan that finds the rows too long for a
 // 16-lane group); same rules as canon_row.
-__device__ __forceinline__ int canon_len(const void* row, int is64, int width, int use_eos, int lane, int G) {
+__device__ __forceinline__ int canon_len(const void* row, int esz, int width, int use_eos, int lane, int G) {
     const int sl = grp_sl(lane, G);
     const bool half = (G == 16);
     const int pa = sl, pb = sl + 16;
     const bool ina = pa < width;
     const bool inb = half && pb < width;
-    const long long ta = ina ? ld_tok(row, is64, pa) : 0ll;
-    const long long tb = inb ? ld_tok(row, is64, pb) : 0ll;
+    const long long ta = ina ? ld_tok(row, esz, pa) : 0ll;
+    const long long tb = inb ? ld_tok(row, esz, pb) : 0ll;
     const bool bada = ina && (ta < -1 || ta > 65534);
     const bool badb = inb && (tb < -1 || tb > 65534);
     const u32 tmask = grp_vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane, G);
@@ -153,15 +155,15 @@ __device__ __forceinline__ int canon_len(const void* row, int is64, int width, i
     return __popc(grp_vote(keepa, keepb, lane, G));
 }
 
-__device__ __forceinline__ bool canon_row(const void* row, int is64, int width, int use_eos, int lane, int G,
+__device__ __forceinline__ bool canon_row(const void* row, int esz, int width, int use_eos, int lane, int G,
                                           u32* tokbuf, u64 key[4], int& L) {
     const int sl = grp_sl(lane, G);
     const bool half = (G == 16);
     const int pa = sl, pb = sl + 16;                       // raw positions this lane owns
     const bool ina = pa < width;
     const bool inb = half && pb < width;
-    const long long ta = ina ? ld_tok(row, is64, pa) : 0ll;
-    const long long tb = inb ? ld_tok(row, is64, pb) : 0ll;
+    const long long ta = ina ? ld_tok(row, esz, pa) : 0ll;
+    const long long tb = inb ? ld_tok(row, esz, pb) : 0ll;
     const bool bada = ina && (ta < -1 || ta > 65534);
     const bool badb = inb && (tb < -1 || tb > 65534);
     // -1 = padding: ends the row, never emitted

@@ -54,6 +54,11 @@ void cst_count_launch(void) { COUNT_LAUNCH(); }
 
 typedef CstDeviceGuard DeviceGuard;
 
+// bytes per token id of a CST_DTYPE_*, 0 if unknown
+static int dtype_bytes(int32_t dtype) {
+    return dtype == CST_DTYPE_I32 ? 4 : dtype == CST_DTYPE_I64 ? 8 : dtype == CST_DTYPE_I16 ? 2 : 0;
+}
+
 // ---------------------------------------------------------------------------
 // df table handle (layout: DfView in cst_common.cuh)
 // ---------------------------------------------------------------------------
@@ -318,7 +323,7 @@ extern "C" int cst_df_lookup(const cst_df_table* t, const uint64_t* keys, int64_
     return CST_OK;
 }
 
-__global__ void k_ngram_counts(const void* __restrict__ rows, int is64, int64_t n_rows, int width, int64_t stride,
+__global__ void k_ngram_counts(const void* __restrict__ rows, int esz, int64_t n_rows, int width, int64_t stride,
                                int use_eos, u64* keys_out, int* counts_out, int* n_out, int* len_out) {
     __shared__ u32 tokbuf[8][32];
     const int lane = threadIdx.x & 31;
@@ -327,8 +332,8 @@ __global__ void k_ngram_counts(const void* __restrict__ rows, int is64, int64_t 
     if (row >= n_rows) return;
     u64 key[4];
     int L;
-    const char* base = reinterpret_cast<const char*>(rows) + (size_t)row * (size_t)stride * (is64 ? 8 : 4);
-    canon_row(base, is64, width, use_eos, lane, 32, tokbuf[warp], key, L);
+    const char* base = reinterpret_cast<const char*>(rows) + (size_t)row * (size_t)stride * (size_t)esz;
+    canon_row(base, esz, width, use_eos, lane, 32, tokbuf[warp], key, L);
     int tf[4];
     bool lead[4];
     row_tf(key, lane, 32, -1, tf, lead);
@@ -357,12 +362,12 @@ extern "C" int cst_ngram_counts(const void* rows, int32_t dtype, int64_t n_rows,
     if (width < 1 || width > CST_MAX_ROW_WIDTH)
         return fail(CST_E_RANGE, "cst_ngram_counts: row width %d outside [1, %d]", width, CST_MAX_ROW_WIDTH);
     if (stride < width) return fail(CST_E_ARG, "cst_ngram_counts: stride < width");
-    if (dtype != CST_DTYPE_I32 && dtype != CST_DTYPE_I64) return fail(CST_E_ARG, "cst_ngram_counts: bad dtype");
+    if (!dtype_bytes(dtype)) return fail(CST_E_ARG, "cst_ngram_counts: bad dtype");
     if (n_rows == 0) return CST_OK;
     DeviceGuard guard(device);
     if (!guard.ok) return fail(CST_E_CUDA, "cst_ngram_counts: cannot select device %d", device);
     const unsigned blocks = (unsigned)((n_rows + 7) / 8);
-    k_ngram_counts<<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, dtype == CST_DTYPE_I64, n_rows, width, stride,
+    k_ngram_counts<<<blocks, 256, 0, (cudaStream_t)stream>>>(rows, dtype_bytes(dtype), n_rows, width, stride,
                                                            use_eos, (u64*)keys_out, counts_out, n_out, len_out);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
@@ -475,12 +480,12 @@ struct ScoreParams {
     const double* gauss;
     const void* cand;
     const void* greedy;
-    int cand_is64;
+    int cand_esz;
     int64_t n_cand;
     int cand_width;
     int64_t cand_stride;
     const void* refs;
-    int ref_is64;
+    int ref_esz;
     int ref_width;
     int64_t ref_stride;
     const int64_t* ref_offsets;
@@ -623,26 +628,26 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                     }
                     {
                         const void* row;
-                        int is64, width;
+                        int esz, width;
                         if (phase == 0) {
-                            is64 = p.ref_is64;
+                            esz = p.ref_esz;
                             width = p.ref_width;
                             row = reinterpret_cast<const char*>(p.refs) +
-                                  (size_t)(c0 + ri) * (size_t)p.ref_stride * (is64 ? 8 : 4);
+                                  (size_t)(c0 + ri) * (size_t)p.ref_stride * (size_t)esz;
                         } else {
                             const bool gq = ri >= p.cands_per_video;
                             const int64_t ci = video * p.cands_per_video + (gq ? ri - p.cands_per_video : ri);
-                            is64 = p.cand_is64;
+                            esz = p.cand_esz;
                             width = p.cand_width;
                             row = reinterpret_cast<const char*>(gq ? p.greedy : p.cand) +
-                                  (size_t)ci * (size_t)p.cand_stride * (is64 ? 8 : 4);
+                                  (size_t)ci * (size_t)p.cand_stride * (size_t)esz;
                         }
                         if (!act) width = 0;                         // idle half of an odd pair
 
                         // ---- front, common to references and candidates ----
                         u64 key[4];
                         int L;
-                        const bool bad = canon_row(row, is64, width, p.use_eos, lane, G, tokbuf, key, L);
+                        const bool bad = canon_row(row, esz, width, p.use_eos, lane, G, tokbuf, key, L);
                         const int sl = grp_sl(lane, G);
                         const bool live = act && L <= G;             // G = 16: longer rows become items of their own
                         if (G == 16) {
@@ -940,8 +945,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
         return fail(CST_E_RANGE, "%s: row widths %d/%d outside [1, %d]", who, cand_width, ref_width,
                     CST_MAX_ROW_WIDTH);
     if (cand_stride < cand_width || ref_stride < ref_width) return fail(CST_E_ARG, "%s: stride < width", who);
-    if ((cand_dtype != CST_DTYPE_I32 && cand_dtype != CST_DTYPE_I64) ||
-        (ref_dtype != CST_DTYPE_I32 && ref_dtype != CST_DTYPE_I64))
+    if (!dtype_bytes(cand_dtype) || !dtype_bytes(ref_dtype))
         return fail(CST_E_ARG, "%s: bad dtype", who);
     if (refs_per_video < 0 || (refs_per_video == 0 && !ref_offsets))
         return fail(CST_E_ARG, "%s: refs_per_video must be > 0", who);
@@ -961,8 +965,8 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     p.gauss = t->gauss;
     p.cand = cand;
     p.greedy = greedy;
-    p.cand_is64 = (cand_dtype == CST_DTYPE_I64);
-    p.ref_is64 = (ref_dtype == CST_DTYPE_I64);
+    p.cand_esz = dtype_bytes(cand_dtype);
+    p.ref_esz = dtype_bytes(ref_dtype);
     p.n_cand = n_cand;
     p.cand_width = cand_width;
     p.cand_stride = cand_stride;
@@ -1107,7 +1111,7 @@ __device__ __forceinline__ bool set_insert_new(u64* keys, u32 mask, u32 idx, u64
 
 // One CTA per video: the set union of its refs' n-grams is formed in shared memory
 // (compute_ciderdf.py:66-67); each member then adds 1 to its global counter (:68).
-__global__ void __launch_bounds__(256) k_df_build(const void* __restrict__ rows, int is64, int width, int64_t stride,
+__global__ void __launch_bounds__(256) k_df_build(const void* __restrict__ rows, int esz, int width, int64_t stride,
                                                   int use_eos, const int64_t* __restrict__ video_offsets,
                                                   int64_t n_videos, u32 set_slots, int set_shift, u64* g_keys,
                                                   u32* g_cnt, u32 g_cap, u32* n_unique, u32* n_bad) {
@@ -1123,8 +1127,8 @@ __global__ void __launch_bounds__(256) k_df_build(const void* __restrict__ rows,
         for (int64_t r = r0 + warp; r < r1; r += nwarps) {
             u64 key[4];
             int L;
-            const char* row = reinterpret_cast<const char*>(rows) + (size_t)r * (size_t)stride * (is64 ? 8 : 4);
-            const bool bad = canon_row(row, is64, width, use_eos, lane, 32, tokbuf, key, L);
+            const char* row = reinterpret_cast<const char*>(rows) + (size_t)r * (size_t)stride * (size_t)esz;
+            const bool bad = canon_row(row, esz, width, use_eos, lane, 32, tokbuf, key, L);
             if (bad && lane == 0) atomicAdd(n_bad, 1u);
             int tf[4];
             bool lead[4];
@@ -1187,7 +1191,7 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     if (width < 1 || width > CST_MAX_ROW_WIDTH)
         return fail(CST_E_RANGE, "cst_df_build_from_rows: row width %d outside [1, %d]", width, CST_MAX_ROW_WIDTH);
     if (stride < width) return fail(CST_E_ARG, "cst_df_build_from_rows: stride < width");
-    if (dtype != CST_DTYPE_I32 && dtype != CST_DTYPE_I64) return fail(CST_E_ARG, "cst_df_build_from_rows: bad dtype");
+    if (!dtype_bytes(dtype)) return fail(CST_E_ARG, "cst_df_build_from_rows: bad dtype");
     if (n_videos > 0x7fffffffLL) return fail(CST_E_RANGE, "cst_df_build_from_rows: too many videos");
     int64_t max_refs = 0;
     if (video_offsets[0] != 0 || video_offsets[n_videos] != n_rows)
@@ -1240,7 +1244,7 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     BUILD_TRY(cudaMemset(counters, 0, 2 * sizeof(u32)));
     BUILD_TRY(cudaMemcpy(d_off, video_offsets, (size_t)(n_videos + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
     BUILD_TRY(cudaFuncSetAttribute(k_df_build, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_df_build<<<grid, 256, smem>>>(rows, dtype == CST_DTYPE_I64, width, stride, use_eos ? 1 : 0, d_off, n_videos,
+    k_df_build<<<grid, 256, smem>>>(rows, dtype_bytes(dtype), width, stride, use_eos ? 1 : 0, d_off, n_videos,
                                     set_slots, set_shift, g_keys, g_cnt, g_cap, counters, counters + 1);
     COUNT_LAUNCH();
     BUILD_TRY(cudaGetLastError());

@@ -191,4 +191,6 @@ def _row_dtype(t):
         return _lib.DTYPE_I32
     if t.dtype == torch.int64:
         return _lib.DTYPE_I64
-    raise ValueError('token rows must be int32 or int64, got %s' % t.dtype)
+    if t.dtype == torch.int16:
+        return _lib.DTYPE_I16
+    raise ValueError('token rows must be int16, int32 or int64, got %s' % t.dtype)

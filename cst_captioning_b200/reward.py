@@ -126,7 +126,7 @@ def _rows_on_device(x, device):
         if x.dtype == np.int64:
             x = _narrow(x)
         t = torch.from_numpy(x).to(device)
-    if t.dtype not in (torch.int32, torch.int64):
+    if t.dtype not in (torch.int16, torch.int32, torch.int64):
         t = t.to(torch.int64)
     if t.dim() != 2:
         raise ValueError('caption rows must be 2-D (captions, tokens)')

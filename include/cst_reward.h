@@ -19,7 +19,7 @@
  *     point fails with CST_E_CUDA.
  *
  * Token rows
- *   A caption is a row of token ids (int32 or int64, row-major, `stride` elements
+ *   A caption is a row of token ids (int16, int32 or int64, row-major, `stride` elements
  *   between rows).  Canonicalisation follows utils.py:135-152 (array_to_str):
  *   the first 0 (<end>) ends the caption and is kept only if use_eos != 0; id 1
  *   (<start>) is dropped wherever it occurs.  Rows may be at most 32 tokens wide
@@ -51,6 +51,7 @@ extern "C" {
 
 #define CST_DTYPE_I32 0
 #define CST_DTYPE_I64 1
+#define CST_DTYPE_I16 2 /* token rows only (ids <= 32767): halves an upload from the host */
 
 /* baseline modes of cst_reward / cst_scb_apply */
 #define CST_BASE_NONE 0        /* reward = score               (utils.py:317-319) */
