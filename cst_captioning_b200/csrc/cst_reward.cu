@@ -614,7 +614,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                         if (!act) ri = 2 * q;
                     } else {
                         if (lane == 0) {
-                            while (*reinterpret_cast<volatile int*>(&s_started[phase]) < n_pairs) { }
+                            while (*reinterpret_cast<volatile int*>(&s_started[phase]) < n_pairs) __nanosleep(32);
                         }
                         __syncwarp();
                         nl = *reinterpret_cast<volatile int*>(&s_nlong[phase]);
@@ -715,10 +715,10 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                             if (!refs_ready) {
                                 if (lane == 0) {
                                     const int np_r = (nref + 1) >> 1;
-                                    while (*reinterpret_cast<volatile int*>(&s_started[0]) < np_r) { }
+                                    while (*reinterpret_cast<volatile int*>(&s_started[0]) < np_r) __nanosleep(32);
                                     const int nlr = *reinterpret_cast<volatile int*>(&s_nlong[0]);
                                     const int total_r = np_r + ((nlr * 2 <= nwarps) ? nlr * 4 : nlr);
-                                    while (*reinterpret_cast<volatile int*>(&s_done_r) < total_r) { }
+                                    while (*reinterpret_cast<volatile int*>(&s_done_r) < total_r) __nanosleep(32);
                                 }
                                 __syncwarp();
                                 refs_ready = true;
