@@ -793,10 +793,12 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
 
         // ---- phase B, spread over the whole CTA (a lone warp would hold 9 idle ones) ----
         // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
+        // (1 / R by reciprocal + multiply: a full double division is ~50 instructions of code
+        // in a kernel that is sensitive to its instruction footprint; the result differs from
+        // the reference's "/ len(refs)" by at most an ulp, the bar is 1e-5)
+        const double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
         for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
-            double s = sc[c] * 0.25;
-            s = (R > 0) ? s / (double)R : 0.0;
-            s *= 10.0;
+            const double s = (sc[c] * 0.25) * inv_R * 10.0;
             sc[c] = s;
             if (p.scores) {
                 const bool is_greedy = c >= p.cands_per_video;
@@ -829,7 +831,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                 for (int i = lane; i < S; i += 32) lowsum += low[i];
                 lowsum = warp_sum(lowsum);                       // same fixed tree in every warp
             }
-            const double base = scb ? lowsum / (double)p.scb_k : 0.0;
+            const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
             for (int i = threadIdx.x; i < S; i += blockDim.x) {
                 const double r = (p.mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
                 p.reward[video * S + i] = (float)r;
