@@ -13,6 +13,10 @@ GOLDEN = os.path.join(ROOT, 'tests', 'golden')
 
 def pytest_configure(config):
     config.addinivalue_line('markers', 'gpu: needs a CUDA device (run on the B200 box)')
+    # the package refuses to import without its CUDA library (no CPU fallback): build it
+    # (nvcc cross-compiles without a GPU) before any test module imports the package
+    import __graft_entry__ as graft
+    graft.build()
 
 
 def pytest_collection_modifyitems(config, items):
