@@ -15,12 +15,12 @@
 #include "cst_reward.h"
 
 #define CRIT_THREADS 256
-#define CRIT_ROWS_PER_ITER 4      /* independent rows in flight per warp */
-
-template <typename ST>
-__device__ __forceinline__ bool tok_positive(const ST* seq_row, int t) {
-    return t == 0 || __ldcs(seq_row + (t - 1)) > 0;
-}
+#ifndef CRIT_ROWS_PER_ITER
+#define CRIT_ROWS_PER_ITER 2      /* rows in flight per warp; measured: 2 rows at 8 CTAs/SM beats 4 rows (spills) and 1 */
+#endif
+#ifndef CRIT_MIN_CTAS
+#define CRIT_MIN_CTAS 8        /* 32 registers: 64 warps per SM */
+#endif
 
 __device__ __forceinline__ double crit_warp_sum(double v) {
 #pragma unroll
@@ -31,7 +31,7 @@ __device__ __forceinline__ double crit_warp_sum(double v) {
 // One warp per row, lane = column (T <= 32 per pass, wider rows loop).  Per-CTA partial
 // sums go to scratch; the last CTA adds them in a fixed order (deterministic loss).
 template <typename ST>
-__global__ void __launch_bounds__(CRIT_THREADS) k_criterion_fwd(
+__global__ void __launch_bounds__(CRIT_THREADS, CRIT_MIN_CTAS) k_criterion_fwd(
     const ST* __restrict__ seq, int64_t seq_stride, const float* __restrict__ logp, int64_t logp_stride,
     const float* __restrict__ reward, int64_t reward_row_stride, int64_t reward_col_stride, int64_t n_rows, int width,
     float* loss_out, float* den_out, u32* ctl, double* partials) {
@@ -42,16 +42,23 @@ __global__ void __launch_bounds__(CRIT_THREADS) k_criterion_fwd(
     const int64_t gw = (int64_t)blockIdx.x * (CRIT_THREADS / 32) + warp;
     double num = 0.0, den = 0.0;
     for (int64_t r0 = gw * CRIT_ROWS_PER_ITER; r0 < n_rows; r0 += warps_total * CRIT_ROWS_PER_ITER) {
+        for (int t = lane; t < width; t += 32) {
+            // all loads of the CRIT_ROWS_PER_ITER rows first, then the arithmetic: the kernel
+            // is a pure stream and lives on the number of loads in flight
+            ST prev[CRIT_ROWS_PER_ITER];
+            float lp[CRIT_ROWS_PER_ITER], rw[CRIT_ROWS_PER_ITER];
 #pragma unroll
-        for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
-            const int64_t i = r0 + q;
-            if (i >= n_rows) break;
-            for (int t = lane; t < width; t += 32) {
-                const bool m = tok_positive(seq + i * seq_stride, t);
-                const float lp = __ldcs(logp + i * logp_stride + t);
-                const float rw = __ldg(reward + i * reward_row_stride + t * reward_col_stride);
-                if (m) {
-                    num += (double)(-lp * rw);
+            for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+                const int64_t i = r0 + q;
+                const bool in = i < n_rows;
+                prev[q] = (in && t > 0) ? __ldcs(seq + i * seq_stride + (t - 1)) : (ST)(in ? 1 : 0);
+                lp[q] = in ? __ldcs(logp + i * logp_stride + t) : 0.0f;
+                rw[q] = in ? __ldg(reward + i * reward_row_stride + t * reward_col_stride) : 0.0f;
+            }
+#pragma unroll
+            for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+                if (prev[q] > 0) {                         // mask: first column, or previous token > 0
+                    num += (double)(-lp[q] * rw[q]);
                     den += 1.0;
                 }
             }
@@ -104,7 +111,7 @@ __global__ void __launch_bounds__(CRIT_THREADS) k_criterion_fwd(
 }
 
 template <typename ST>
-__global__ void __launch_bounds__(CRIT_THREADS) k_criterion_bwd(
+__global__ void __launch_bounds__(CRIT_THREADS, CRIT_MIN_CTAS) k_criterion_bwd(
     const ST* __restrict__ seq, int64_t seq_stride, const float* __restrict__ reward, int64_t reward_row_stride,
     int64_t reward_col_stride, const float* __restrict__ den, const float* __restrict__ grad_out, int64_t n_rows,
     int width, float* grad_logp, int64_t grad_stride) {
@@ -113,14 +120,20 @@ __global__ void __launch_bounds__(CRIT_THREADS) k_criterion_bwd(
     const int64_t gw = (int64_t)blockIdx.x * (CRIT_THREADS / 32) + warp;
     const float scale = -(*grad_out) / (*den);
     for (int64_t r0 = gw * CRIT_ROWS_PER_ITER; r0 < n_rows; r0 += warps_total * CRIT_ROWS_PER_ITER) {
+        for (int t = lane; t < width; t += 32) {
+            ST prev[CRIT_ROWS_PER_ITER];
+            float rw[CRIT_ROWS_PER_ITER];
 #pragma unroll
-        for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
-            const int64_t i = r0 + q;
-            if (i >= n_rows) break;
-            for (int t = lane; t < width; t += 32) {
-                const bool m = tok_positive(seq + i * seq_stride, t);
-                const float rw = __ldg(reward + i * reward_row_stride + t * reward_col_stride);
-                __stcs(grad_logp + i * grad_stride + t, m ? scale * rw : 0.0f);
+            for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+                const int64_t i = r0 + q;
+                const bool in = i < n_rows;
+                prev[q] = (in && t > 0) ? __ldcs(seq + i * seq_stride + (t - 1)) : (ST)1;
+                rw[q] = in ? __ldg(reward + i * reward_row_stride + t * reward_col_stride) : 0.0f;
+            }
+#pragma unroll
+            for (int q = 0; q < CRIT_ROWS_PER_ITER; ++q) {
+                const int64_t i = r0 + q;
+                if (i < n_rows) __stcs(grad_logp + i * grad_stride + t, prev[q] > 0 ? scale * rw[q] : 0.0f);
             }
         }
     }
