@@ -121,3 +121,50 @@ class CiderD:
         scores = self.score_rows(torch.from_numpy(cand).to(dev), refset, per, use_eos=1)
         arr = scores.cpu().numpy()
         return np.mean(arr), arr
+
+
+class Cider:
+    """``pycocoevalcap.cider.cider.Cider`` (corpus mode) with the string protocol of
+    ``compute_scores.py:67-68, 92``: ``compute_score(gts, res)`` with both dicts keyed by
+    image id and ``res[id]`` a one-element list.  The document frequency is rebuilt on the
+    device from the references of THIS call (``ref_len = log(number of images)``), then
+    every hypothesis is scored with the same kernel as the RL path.
+
+    The strings must be space-joined token ids (what ``utils.array_to_str`` emits); the
+    reference's ``compute_scores.py`` feeds raw words, which have to be mapped to ids
+    first (any injective word -> id map gives the same scores).
+    """
+
+    def __init__(self, n=4, sigma=6.0, device=None):
+        if n != 4 or float(sigma) != 6.0:
+            raise ValueError('the sm_100a kernels implement n=4, sigma=6.0 (the reference defaults)')
+        self._device = torch.device(device if device is not None else 'cuda')
+
+    def compute_score(self, gts, res):
+        from .reward import RefSet
+        assert gts.keys() == res.keys()
+        ids = list(gts.keys())
+        width = _lib.MAX_ROW_WIDTH
+        counts, ref_rows = [], []
+        cand = np.full((len(ids), width), -1, dtype=np.int32)
+        for i, key in enumerate(ids):
+            hyp, refs = res[key], gts[key]
+            assert type(hyp) is list and len(hyp) == 1
+            assert type(refs) is list and len(refs) > 0
+            toks = _parse(hyp[0], width)
+            cand[i, :len(toks)] = toks
+            counts.append(len(refs))
+            for r in refs:
+                row = np.full(width, -1, dtype=np.int32)
+                toks = _parse(r, width)
+                row[:len(toks)] = toks
+                ref_rows.append(row)
+        dev = self._device
+        rows = torch.from_numpy(np.stack(ref_rows)).to(dev)
+        offsets = np.concatenate([[0], np.cumsum(counts)])
+        table = DfTable.from_rows(rows, video_offsets=offsets, use_eos=1)
+        scorer = CiderD(df=table)
+        refset = RefSet(rows, per_video=counts[0]) if len(set(counts)) == 1 else RefSet(rows, offsets=offsets)
+        arr = scorer.score_rows(torch.from_numpy(cand).to(dev), refset, 1, use_eos=1).cpu().numpy()
+        table.close()
+        return np.mean(arr), arr
