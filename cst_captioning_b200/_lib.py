@@ -18,7 +18,7 @@ BASE_NONE, BASE_GREEDY, BASE_SCB_GT, BASE_SCB_SAMPLE = 0, 1, 2, 3
 MAX_ROW_WIDTH = 32
 MAX_TOKEN_ID = 65534
 NGRAM_SLOTS_PER_ROW = 128
-N_STATS = 5
+N_STATS = 7
 
 # every symbol include/cst_reward.h declares: name -> (restype, argtypes)
 _vp, _i32, _i64, _f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_double

@@ -467,6 +467,8 @@ __device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* parti
         stats[2] = n_m;
         stats[3] = n_b;
         stats[4] = (double)atomicExch(&ctl[1], 0u);
+        stats[5] = tm / n_m;      // m_score and b_score of THIS launch, so a single-GPU caller
+        stats[6] = tb / n_b;      // needs no follow-up kernel (ranks re-derive them from the sums)
         __threadfence();
         ctl[0] = 0u;
     }

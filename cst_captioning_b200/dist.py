@@ -41,8 +41,9 @@ def shard_batch(model_res, data_gts, seq_per_img, rank, world, bcmrscores=None, 
 
 
 def all_reduce_stats(stats, group=None):
-    """Sum the statistics ``[sum_m, sum_b, n_m, n_b, bad_rows]`` over ranks, in place, on
-    the current stream (NCCL) -- the one collective of the path."""
+    """Sum the statistics ``[sum_m, sum_b, n_m, n_b, bad_rows, ...]`` over ranks, in place, on
+    the current stream (NCCL) -- the one collective of the path.  (Entries 5 and 6, the
+    per-launch means, are meaningless after the sum: use :func:`means`.)"""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=group)
     return stats

@@ -94,6 +94,8 @@ class HostRewardPipeline:
                 out[lo * s:hi * s].copy_(rew[:, 0], non_blocking=True)
                 rew.record_stream(self.out_stream)
             done.append(rew)
+        total[5] = total[0] / total[2]              # means of the whole batch (the slices' own means were summed)
+        total[6] = total[1] / total[3]
         main.wait_stream(self.out_stream)
         for b in bufs:
             b['used'] = False

@@ -62,7 +62,7 @@ extern "C" {
 #define CST_MAX_ROW_WIDTH 32
 #define CST_MAX_TOKEN_ID 65534
 #define CST_NGRAM_SLOTS_PER_ROW 128 /* 4 orders x 32 positions */
-#define CST_N_STATS 5
+#define CST_N_STATS 7
 
 typedef struct cst_df_table cst_df_table;
 
@@ -187,7 +187,8 @@ int64_t cst_reward_scratch_bytes(int64_t n_groups);
  *               consensus scores (dataloader.py:142-144), CST_BASE_SCB_GT only
  *   reward_out  [dev] float32 n_cand: the column the reference repeats T times
  *               (utils.py:224, 321-322) and casts to float (train.py:209)
- *   stats_out   [dev] float64[CST_N_STATS] = { sum_m, sum_b, n_m, n_b, n_bad_rows }:
+ *   stats_out   [dev] float64[CST_N_STATS] = { sum_m, sum_b, n_m, n_b, n_bad_rows,
+ *               m_score, b_score }:
  *               m_score = sum_m / n_m, b_score = sum_b / n_b as returned at
  *               utils.py:226, 324 (sums, so ranks can all-reduce them);
  *               n_bad_rows counts rows with ids outside [0, 65534].
