@@ -109,6 +109,27 @@ class ClockSampler:
                 'reasons': sorted(self.reasons), 'samples': len(self.samples)}
 
 
+def bind_to_gpu_numa_node(index):
+    """Pin this rank to the CPUs NVML reports as local to its GPU, so the pinned host buffers
+    of the end-to-end leg are allocated on that socket (8 ranks uploading through the wrong
+    socket halve the aggregate PCIe rate).  Best effort."""
+    try:
+        import math
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, math.ceil((os.cpu_count() or 64) / 64))
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        allowed = set(os.sched_getaffinity(0))
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return 0
+
+
 def measured_peak():
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     try:
@@ -229,6 +250,7 @@ def product_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit('bench.py: no CUDA device; the reward path has no CPU fallback')
     torch.cuda.set_device(local)
+    bind_to_gpu_numa_node(local)       # before any pinned allocation: first touch decides the NUMA node
     dev = torch.device('cuda', local)
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
@@ -299,7 +321,7 @@ def product_arm(args):
     # ---- end to end through the public API with HOST buffers -----------------------
     e2e_steps = max(3, min(args.steps, 10))
     out_pin = torch.empty(n_cap, dtype=torch.float32).pin_memory()
-    st_pin = torch.empty(5, dtype=torch.float64).pin_memory()
+    st_pin = torch.empty(7, dtype=torch.float64).pin_memory()       # CST_N_STATS
 
     pipe = cst.HostRewardPipeline(scorer, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1,
                                   slices=args.e2e_slices)
