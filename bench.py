@@ -111,8 +111,8 @@ class ClockSampler:
 
 def bind_to_gpu_numa_node(index):
     """Pin this rank to the CPUs NVML reports as local to its GPU, so the pinned host buffers
-    of the end-to-end leg are allocated on that socket (8 ranks uploading through the wrong
-    socket halve the aggregate PCIe rate).  Best effort."""
+    of the end-to-end leg are first-touched on that socket.  Best effort; a no-op on the
+    measured pool, whose boxes expose one NUMA node (profiles/r1k_h2d_scaling_n8.jsonl)."""
     try:
         import math
         import pynvml
