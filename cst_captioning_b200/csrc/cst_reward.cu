@@ -1003,11 +1003,17 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     const u32 worst = (u32)p.chunk_refs * (u32)grams_per_row(ref_width);
     p.tab_slots = worst + worst / 4 + 8;
     if (p.tab_slots < 64) p.tab_slots = 64;
+#ifdef CST_EXPERIMENT
+    if (const char* e = getenv("CST_EXP_SLOTS")) p.tab_slots = (u32)atoi(e);
+#endif
 
     const int n_local = cands_per_video * (greedy ? 2 : 1);
     int nwarps = ((p.chunk_refs > n_local ? p.chunk_refs : n_local) + 1) / 2;   // two rows per warp
     if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
     if (nwarps < 4) nwarps = 4;
+#ifdef CST_EXPERIMENT
+    if (const char* e = getenv("CST_EXP_WARPS")) nwarps = atoi(e);
+#endif
     const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
                         (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
                         (size_t)cands_per_video * sizeof(double) + (size_t)4 * n_local * sizeof(double) +

@@ -24,7 +24,8 @@ def cst():
 
 
 @pytest.mark.parametrize('n,t,dtype', [(7, 5, torch.int64), (1280, 28, torch.int64), (4099, 28, torch.int32),
-                                       (33, 40, torch.int64)])
+                                       (33, 40, torch.int64), (5, 3, torch.int64), (1, 1, torch.int32),
+                                       (3, 7, torch.int32), (70001, 27, torch.int64), (300000, 28, torch.int64)])
 def test_forward_backward_match_torch(cst, n, t, dtype):
     dev = torch.device('cuda:0')
     g = torch.Generator(device='cpu').manual_seed(n * 31 + t)
@@ -50,6 +51,20 @@ def test_forward_backward_match_torch(cst, n, t, dtype):
     a = crit(seq, logp.detach(), col).item()
     b = crit(seq, logp.detach(), col).item()
     assert a == b
+    # row-strided views (a slice of a wider buffer) take the row-per-warp kernels; dense (N, T)
+    # tensors the element-stream kernels: both must give the same loss and gradient
+    wide_seq = torch.zeros(n, t + 3, dtype=seq.dtype, device=dev)
+    wide_seq[:, :t] = seq
+    wide_lp = torch.zeros(n, t + 5, device=dev)
+    wide_lp[:, :t] = logp.detach()
+    lp_view = wide_lp[:, :t].requires_grad_(True)
+    loss_v = crit(wide_seq[:, :t], lp_view, col)
+    g_v, = torch.autograd.grad(loss_v, lp_view)
+    lp_d = logp.detach().clone().requires_grad_(True)
+    loss_d = crit(seq, lp_d, col)
+    g_d, = torch.autograd.grad(loss_d, lp_d)
+    np.testing.assert_allclose(loss_v.item(), loss_d.item(), rtol=1e-6, atol=1e-8)
+    assert torch.equal(g_v, g_d) or torch.allclose(g_v, g_d, rtol=1e-6, atol=1e-12)
 
 
 def test_reward_path_feeds_the_criterion(cst):

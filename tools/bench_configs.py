@@ -49,6 +49,16 @@ b = synth.make_batch(64, 20, 20, seed=12, greedy=True)
 c, gr, r = (torch.from_numpy(b[k]).to(dev) for k in ('sampled', 'greedy', 'refs'))
 ms = timed(lambda: cst.get_self_critical_reward(c, gr, r, scorer, expand_feat=1, seq_per_img=20, use_eos=1), 200)
 out['config3: 1280 sampled + 1280 greedy, reward = sample - greedy'] = {'ms_per_call': ms, 'captions_per_s': 2560 / ms * 1e3}
+# the same call captured once in a CUDA graph and replayed (what a launch-bound training loop would do)
+side = torch.cuda.Stream(dev)
+with torch.cuda.stream(side):
+    cst.get_self_critical_reward(c, gr, r, scorer, expand_feat=1, seq_per_img=20, use_eos=1)
+side.synchronize()
+graph = torch.cuda.CUDAGraph()
+with torch.cuda.graph(graph, stream=side):
+    keep = cst.get_self_critical_reward(c, gr, r, scorer, expand_feat=1, seq_per_img=20, use_eos=1)
+ms = timed(graph.replay, 200)
+out['config3, CUDA-graph replay'] = {'ms_per_call': ms, 'captions_per_s': 2560 / ms * 1e3}
 
 b = synth.make_batch(512, 20, 20, seed=13)
 c, r = torch.from_numpy(b['sampled']).to(dev), torch.from_numpy(b['refs']).to(dev)
