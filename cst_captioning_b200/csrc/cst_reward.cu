@@ -509,6 +509,10 @@ struct ScoreParams {
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
+/* shared memory ahead of the per-video table: invn, gh_all, red, lenr, long_r, tok_all (see k_score) */
+#define CST_SCORE_FIXED_SMEM ((128 + CST_MAX_WARPS * 64 + 2 * CST_MAX_WARPS) * sizeof(double) + \
+                              64 * sizeof(int) + CST_MAX_WARPS * 32 * sizeof(u32))
+static_assert(CST_SCORE_FIXED_SMEM % 16 == 0, "the per-video table must stay 16-byte aligned");
 #ifndef CST_MIN_CTAS
 #define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
 #endif
@@ -533,17 +537,20 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
     const int nwarps = blockDim.x >> 5;
     const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
 
-    VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
-    double* invn = reinterpret_cast<double*>(tab + p.tab_slots);   // [4][32]
-    double* gh_all = invn + 128;                                    // [nwarps][2][32]
-    double* sc = gh_all + nwarps * 64;                              // [n_local]
+    // Fixed-size arrays first, then the table, then the arrays sized by the candidate count: what the
+    // item loop touches sits at compile-time offsets (the address arithmetic folds into the
+    // instructions instead of being recomputed from tab_slots under register pressure).
+    double* invn = reinterpret_cast<double*>(smem);                 // [4][32]
+    double* gh_all = invn + 128;                                    // [CST_MAX_WARPS][2][32]
+    double* red = gh_all + CST_MAX_WARPS * 64;                      // [2 * CST_MAX_WARPS]
+    int* lenr = reinterpret_cast<int*>(red + 2 * CST_MAX_WARPS);    // [32]
+    int* long_r = lenr + 32;                                        // [32] long reference rows of the chunk
+    u32* tok_all = reinterpret_cast<u32*>(long_r + 32);             // [CST_MAX_WARPS][32]
+    VidSlot* tab = reinterpret_cast<VidSlot*>(tok_all + CST_MAX_WARPS * 32);   // [tab_slots], 16-byte aligned
+    double* sc = reinterpret_cast<double*>(tab + p.tab_slots);      // [n_local]
     double* low = sc + n_local;                                     // [cands_per_video]
     double* part = low + p.cands_per_video;                         // [n_local][4] long-row partial scores
-    double* red = part + 4 * n_local;                               // [2 * nwarps]
-    int* lenr = reinterpret_cast<int*>(red + 2 * nwarps);           // [32]
-    int* long_r = lenr + 32;                                        // [32] long reference rows of the chunk
-    int* long_c = long_r + 32;                                      // [n_local] long candidate rows
-    u32* tok_all = reinterpret_cast<u32*>(long_c + n_local);        // [nwarps][32]
+    int* long_c = reinterpret_cast<int*>(part + 4 * n_local);       // [n_local] long candidate rows
     double* gh = gh_all + warp * 64;
     u32* tokbuf = tok_all + warp * 32;
 
@@ -1014,11 +1021,9 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
 #ifdef CST_EXPERIMENT
     if (const char* e = getenv("CST_EXP_WARPS")) nwarps = atoi(e);
 #endif
-    const size_t smem = (size_t)p.tab_slots * sizeof(VidSlot) + 128 * sizeof(double) +
-                        (size_t)nwarps * 64 * sizeof(double) + (size_t)n_local * sizeof(double) +
-                        (size_t)cands_per_video * sizeof(double) + (size_t)4 * n_local * sizeof(double) +
-                        (size_t)2 * nwarps * sizeof(double) + (64 + (size_t)n_local) * sizeof(int) +
-                        (size_t)nwarps * 32 * sizeof(u32);
+    const size_t smem = CST_SCORE_FIXED_SMEM + (size_t)p.tab_slots * sizeof(VidSlot) +
+                        (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
+                        (size_t)4 * n_local * sizeof(double) + (size_t)n_local * sizeof(int);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 
     const int threads = nwarps * 32;
