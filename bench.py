@@ -318,6 +318,36 @@ def product_arm(args):
                 'kernel_ms': kern_ms, 'bytes_per_caption': BYTES_PER_CAPTION, 'peak_source': peak_src,
                 'frac_of_nominal_8TBs': achieved / 8000.0}
 
+    # ---- informational: references staged once (CookedRefs) -------------------------
+    # The ground-truth captions of a training set never change, so their half of the kernel can be
+    # run once and kept in HBM; a step then passes candidates + video indices.  NOT the headline
+    # (that one, like the reference, works the refs up from raw rows every step).
+    staged = None
+    if not args.no_staged:
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        cooked = cst.CookedRefs.cook(d_refs, scorer, use_eos=1)      # first call: module load
+        del cooked
+        c0.record()
+        cooked = cst.CookedRefs.cook(d_refs, scorer, use_eos=1)
+        c1.record()
+        cooked_b = cooked.batch(torch.arange(n_videos, device=dev))
+        for _ in range(3):
+            rew_c, _, _, stats_c = cst.get_cst_reward(d_cand, cooked_b, scorer, **kw)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(args.steps):
+            rew_c, _, _, stats_c = cst.get_cst_reward(d_cand, cooked_b, scorer, **kw)
+        s1.record()
+        barrier()
+        ms_c = s0.elapsed_time(s1) / args.steps
+        staged = {'value': n_cap / (ms_c * 1e-3), 'unit': UNIT + ' per GPU', 'ms_per_step': ms_c,
+                  'cook_ms_once': c0.elapsed_time(c1), 'image_bytes_per_video': cooked.stride,
+                  'images_bytes_total': cooked.nbytes(),
+                  'same_bits_as_raw_rows': bool(torch.equal(rew_c, rew)),
+                  'note': 'cst_refs_cook once outside the timed region, then cst_reward_cooked per step'}
+        del cooked, cooked_b
+
     # ---- end to end through the public API with HOST buffers -----------------------
     e2e_steps = max(3, min(args.steps, 10))
     out_pin = torch.empty(n_cap, dtype=torch.float32).pin_memory()
@@ -385,7 +415,7 @@ def product_arm(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
             'config': workload_config(n_videos, world), 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e,
-            'gpu_launches': int(launches), 'clocks': clocks.summary(),
+            'gpu_launches': int(launches), 'clocks': clocks.summary(), 'staged_refs': staged,
             'check': {'m_score': float(stats[0] / stats[2]), 'b_score': float(stats[1] / stats[3]),
                       'bad_rows': float(stats[4]), 'df_ngrams': len(table)},
         }
@@ -404,6 +434,7 @@ def main():
     ap.add_argument('--videos', type=int, default=65536, help='videos per GPU per step')
     ap.add_argument('--cpu-videos', type=int, default=640, help='CPU-baseline sample size (videos)')
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-staged', action='store_true', help='skip the informational staged-references leg')
     ap.add_argument('--e2e-slices', type=int, default=16, help='video slices of the host pipeline')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -8,6 +8,7 @@ Public surface (mirrors the reference's interfaces for this path):
 * :func:`get_self_critical_reward`     <- ``utils.get_self_critical_reward`` (``utils.py:169``)
 * :class:`DfTable`                     <- the ``*_ciderdf.pkl`` of ``compute_ciderdf.py``
 * :class:`RefSet`                      device-resident reference rows
+* :class:`CookedRefs`                  references staged once (the kernel's reference half kept in HBM)
 * :class:`RewardCriterion`             <- ``model.RewardCriterion`` (``model.py:7-23``), fused fwd/bwd
 * :class:`HostRewardPipeline`          the same reward for pinned host batches (upload overlapped with scoring)
 
@@ -18,6 +19,6 @@ been built: there is no CPU fallback.
 from ._lib import CstError, LIB_PATH, lib          # noqa: F401  (loads the .so)
 from .df_table import DfTable, pack_ngrams, unpack_keys  # noqa: F401
 from .ciderd import Cider, CiderD                   # noqa: F401
-from .reward import RefSet, RefStore, get_cst_reward, get_self_critical_reward  # noqa: F401
+from .reward import CookedRefs, RefSet, RefStore, get_cst_reward, get_self_critical_reward  # noqa: F401
 from .pipeline import HostRewardPipeline            # noqa: F401
 from .criterion import RewardCriterion              # noqa: F401

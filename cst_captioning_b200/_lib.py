@@ -43,6 +43,12 @@ SYMBOLS = {
     'cst_reward_scratch_bytes': (_i64, [_i64]),
     'cst_reward': (C.c_int, [_vp] + _ROWS + [_i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     'cst_reward_noalloc': (C.c_int, [_vp] + _ROWS + [_i32, _i32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    'cst_refs_cooked_bytes': (_i64, [_i32, _i32]),
+    'cst_refs_cook': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i64, _vp, _i32, _i64, _i32, _vp, _i64, _vp, _vp]),
+    'cst_reward_cooked': (C.c_int, [_vp, _vp, _vp, _i32, _i64, _i32, _i64,      # table, cand, greedy, dtype, n, width, stride
+                                    _vp, _i64, _vp, _i32, _i32, _i64,            # images, stride, index, ref_width, refs/video, n_videos
+                                    _i32, _i32, _i32, _i32, _i32, _vp,           # cands/video, use_eos, mode, seq_per_img, scb_k, bcmr
+                                    _vp, _vp, _vp, _vp, _i64, _vp]),             # reward, scores, stats, scratch, bytes, stream
     'cst_criterion_scratch_bytes': (_i64, []),
     'cst_reward_criterion_fwd': (C.c_int, [_vp, _i32, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _i64,
                                            C.c_int, _vp]),

@@ -475,6 +475,34 @@ __device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* parti
 }
 
 // ---------------------------------------------------------------------------
+// bulk asynchronous copy global -> shared (the TMA engine's 1-D form) completing on an mbarrier
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, u32 arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// one thread: expect `bytes`, then start the copy; earlier generic-proxy accesses of the
+// destination are ordered before the engine's writes by the proxy fence
+__device__ __forceinline__ void bulk_fetch(void* dst, const void* src, u32 bytes, unsigned long long* bar) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, u32 parity) {
+    u32 ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+// ---------------------------------------------------------------------------
 // fused scoring kernel
 // ---------------------------------------------------------------------------
 struct ScoreParams {
@@ -503,16 +531,26 @@ struct ScoreParams {
     double* scores;
     double* stats;
     u32* ctl;
+    u32* bad_out;         // += rows holding ids outside [-1, 65534] (= ctl + 1 when there is scratch)
     double* partials;
     double n_m, n_b;
     u32 tab_slots;        // capacity of the per-video shared table
+    // staged references (cst_refs_cook): the result of phase R kept in HBM, one image per video
+    const unsigned char* cooked;    // scoring from images: phase R becomes a copy
+    const int64_t* cooked_index;    // image of video v = cooked_index[v] (NULL: v)
+    int64_t cooked_stride;          // bytes per image
+    unsigned char* cook_out;        // cooking: no candidates, phase R's result is written out
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
-/* shared memory ahead of the per-video table: invn, gh_all, red, lenr, long_r, tok_all (see k_score) */
-#define CST_SCORE_FIXED_SMEM ((128 + CST_MAX_WARPS * 64 + 2 * CST_MAX_WARPS) * sizeof(double) + \
-                              64 * sizeof(int) + CST_MAX_WARPS * 32 * sizeof(u32))
-static_assert(CST_SCORE_FIXED_SMEM % 16 == 0, "the per-video table must stay 16-byte aligned");
+/* shared memory ahead of the per-video table (see k_score): gh_all, red, long_r, tok_all, then the part that
+   a staged-reference image mirrors byte for byte: hdr, invn, lenr and, right behind them, the table */
+#define CST_SCORE_WORK_SMEM ((CST_MAX_WARPS * 64 + 2 * CST_MAX_WARPS) * sizeof(double) + 32 * sizeof(int) + \
+                             CST_MAX_WARPS * 32 * sizeof(u32))
+#define CST_IMG_HEAD (4 * sizeof(u32) + 128 * sizeof(double) + 32 * sizeof(int))   /* hdr + invn + lenr */
+#define CST_SCORE_FIXED_SMEM (CST_SCORE_WORK_SMEM + CST_IMG_HEAD)
+#define CST_IMG_MAGIC 0x43535431u   /* "CST1": layout version of a staged-reference image */
+static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_IMG_HEAD % 16 == 0, "the image must stay 16-byte aligned");
 #ifndef CST_MIN_CTAS
 #define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
 #endif
@@ -525,12 +563,20 @@ static_assert(CST_SCORE_FIXED_SMEM % 16 == 0, "the per-video table must stay 16-
 // a few rows are long, one n-gram ORDER of a row per warp, so the extra pass is short
 // for the whole CTA.  Keeping a single copy matters: the kernel was instruction-fetch
 // bound when the four combinations were separate instantiations.
+// MODE: which phases a launch runs.  The raw-row kernel (both phases) is sensitive to its instruction
+// footprint, so the two staged-reference variants are separate instantiations that drop the
+// other phase's code instead of branches inside it.
+#define CST_MODE_RAW 0      /* phase R from the reference rows, phase C, phase B */
+#define CST_MODE_STAGED 1   /* phase R replaced by the copy of the video's image (cst_refs_cook) */
+#define CST_MODE_COOK 2     /* phase R only; its result is written out as the video's image */
+template <int MODE>
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
     __shared__ int s_ticket[2];                      // next item of the phase's work list
     __shared__ int s_started[2];                     // pair items past their canonicalisation
     __shared__ int s_done_r;                         // reference items fully published
+    __shared__ unsigned long long s_img_bar;         // staged references: completion of the image fetch
     __shared__ double s_gauss[CST_GAUSS_N];          // length-penalty LUT (a global load here would be an L2 trip)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -540,13 +586,15 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
     // Fixed-size arrays first, then the table, then the arrays sized by the candidate count: what the
     // item loop touches sits at compile-time offsets (the address arithmetic folds into the
     // instructions instead of being recomputed from tab_slots under register pressure).
-    double* invn = reinterpret_cast<double*>(smem);                 // [4][32]
-    double* gh_all = invn + 128;                                    // [CST_MAX_WARPS][2][32]
+    double* gh_all = reinterpret_cast<double*>(smem);               // [CST_MAX_WARPS][2][32]
     double* red = gh_all + CST_MAX_WARPS * 64;                      // [2 * CST_MAX_WARPS]
-    int* lenr = reinterpret_cast<int*>(red + 2 * CST_MAX_WARPS);    // [32]
-    int* long_r = lenr + 32;                                        // [32] long reference rows of the chunk
+    int* long_r = reinterpret_cast<int*>(red + 2 * CST_MAX_WARPS);  // [32] long reference rows of the chunk
     u32* tok_all = reinterpret_cast<u32*>(long_r + 32);             // [CST_MAX_WARPS][32]
-    VidSlot* tab = reinterpret_cast<VidSlot*>(tok_all + CST_MAX_WARPS * 32);   // [tab_slots], 16-byte aligned
+    // hdr .. tab is what phase R produces: contiguous, so a staged-reference image is one copy
+    u32* hdr = tok_all + CST_MAX_WARPS * 32;                        // [4] magic, tab_slots, refs, use_eos
+    double* invn = reinterpret_cast<double*>(hdr + 4);              // [4][32]
+    int* lenr = reinterpret_cast<int*>(invn + 128);                 // [32]
+    VidSlot* tab = reinterpret_cast<VidSlot*>(lenr + 32);           // [tab_slots], 16-byte aligned
     double* sc = reinterpret_cast<double*>(tab + p.tab_slots);      // [n_local]
     double* low = sc + n_local;                                     // [cands_per_video]
     double* part = low + p.cands_per_video;                         // [n_local][4] long-row partial scores
@@ -556,6 +604,11 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
 
     for (int i = threadIdx.x; i < CST_GAUSS_N; i += blockDim.x) s_gauss[i] = p.gauss[i];
     // (visible to the CTA after the __syncthreads that follows the first table clear)
+    u32 img_parity = 0;
+    if (MODE == CST_MODE_STAGED) {
+        if (threadIdx.x == 0) mbar_init(&s_img_bar, 1);
+        __syncthreads();
+    }
 
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
 #ifdef CST_PHASE_TIMING
@@ -573,15 +626,27 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
             r0 = video * p.refs_per_video;
             r1 = r0 + p.refs_per_video;
         }
-        const int R = (int)(r1 - r0);
+        int R = (int)(r1 - r0);
         for (int c = threadIdx.x; c < n_local; c += blockDim.x) sc[c] = 0.0;
         u32 bad_rows = 0;
+        bool bad_image = false;
 
         for (int64_t c0 = r0; c0 < r1; c0 += p.chunk_refs) {
-            const int nref = (int)((r1 - c0) < (int64_t)p.chunk_refs ? (r1 - c0) : (int64_t)p.chunk_refs);
-            {   // clear the video table and the work-list counters
-                uint4* z = reinterpret_cast<uint4*>(tab);
-                for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+            int nref = (int)((r1 - c0) < (int64_t)p.chunk_refs ? (r1 - c0) : (int64_t)p.chunk_refs);
+            {   // clear the video table (or fetch the staged one) and reset the work-list counters
+                if (MODE == CST_MODE_STAGED) {
+                    // one bulk copy by the copy engine: header, ref norms, ref lengths and table land
+                    // while the warps canonicalise and look up their candidates (the wait is where
+                    // phase C otherwise waits for the reference items)
+                    if (threadIdx.x == 0) {
+                        const int64_t img = p.cooked_index ? p.cooked_index[video] : video;
+                        bulk_fetch(hdr, p.cooked + (size_t)img * (size_t)p.cooked_stride,
+                                   (u32)CST_IMG_HEAD + p.tab_slots * (u32)sizeof(VidSlot), &s_img_bar);
+                    }
+                } else {
+                    uint4* z = reinterpret_cast<uint4*>(tab);
+                    for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
+                }
                 if (threadIdx.x < 2) {
                     s_nlong[threadIdx.x] = 0;
                     s_ticket[threadIdx.x] = 0;
@@ -594,7 +659,8 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
             bool refs_ready = false;                     // warp-uniform
 
 #pragma unroll 1
-            for (int phase = 0; phase < 2; ++phase) {
+            for (int phase = (MODE == CST_MODE_STAGED) ? 1 : 0; phase < ((MODE == CST_MODE_COOK) ? 1 : 2); ++phase) {
+                const bool is_r = (MODE == CST_MODE_COOK) || (MODE == CST_MODE_RAW && phase == 0);
                 // One dynamic work list per phase: first the row pairs (two rows per warp, lane groups
                 // of 16), then the rows the pairs found too long for 16 lanes -- a long row is one item
                 // or, when few rows are long, four items (one n-gram order each).  Warps draw tickets,
@@ -603,8 +669,8 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                 // (s_started == n_pairs); a warp that wants a long-row item waits for that, which is
                 // brief and cannot deadlock: pair tickets are all drawn before any long-row ticket, and
                 // a pair item reaches that point without waiting on anybody.
-                const int n_items = phase ? n_local : nref;
-                int* long_list = phase ? long_c : long_r;
+                const int n_items = is_r ? nref : n_local;
+                int* long_list = is_r ? long_r : long_c;
                 const int n_pairs = (n_items + 1) >> 1;
                 int nl = 0;
                 bool split = false;
@@ -638,7 +704,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                     {
                         const void* row;
                         int esz, width;
-                        if (phase == 0) {
+                        if (is_r) {
                             esz = p.ref_esz;
                             width = p.ref_width;
                             row = reinterpret_cast<const char*>(p.refs) +
@@ -688,7 +754,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                         const double inv = inv_norm_of(group_sum4_transposed(n2, lane, G));   // own order's 1/norm
                         const int o = group_order(lane, G);
 
-                        if (phase == 0) {
+                        if (is_r) {
                             // ---- phase R: publish the row into the video table ----
                             const u32 bit = 1u << ri;
 #pragma unroll
@@ -721,7 +787,15 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                             // items has already done the table-independent half of this candidate item
                             // above; here it waits until every reference item has been published.  Reference
                             // items never wait on candidate items, so this cannot deadlock.
-                            if (!refs_ready) {
+                            if (MODE == CST_MODE_STAGED && !refs_ready) {
+                                // phase R was run once, by cst_refs_cook: wait for its image instead
+                                while (!mbar_try_wait(&s_img_bar, img_parity)) {}
+                                bad_image = hdr[0] != CST_IMG_MAGIC || hdr[1] != p.tab_slots ||
+                                            hdr[3] != (u32)p.use_eos;
+                                nref = bad_image ? 0 : (int)hdr[2];
+                                refs_ready = true;
+                            }
+                            if (MODE != CST_MODE_STAGED && !refs_ready) {
                                 if (lane == 0) {
                                     const int np_r = (nref + 1) >> 1;
                                     while (*reinterpret_cast<volatile int*>(&s_started[0]) < np_r) __nanosleep(32);
@@ -783,13 +857,13 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                         }
                     }
                 }
-                if (phase == 0) {                         // no barrier here: see the wait in phase C
+                if (MODE == CST_MODE_RAW && phase == 0) {   // no barrier here: see the wait in phase C
                     CST_TICK(2);
                     continue;
                 }
                 __syncthreads();
                 nl = s_nlong[phase];
-                if (phase == 1 && nl > 0) {
+                if (!is_r && nl > 0) {
                     for (int i = threadIdx.x; i < nl; i += blockDim.x)           // fixed order: deterministic
                         sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
                     __syncthreads();                     // all probes done before the table is cleared again
@@ -797,15 +871,47 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
                 CST_TICK(2 + phase);
             }
         }
+        if (MODE == CST_MODE_STAGED) {
+            // every thread observes the fetch (warps that had no candidate item have not yet) and takes
+            // the video's ref count from the image
+            while (!mbar_try_wait(&s_img_bar, img_parity)) {}
+            img_parity ^= 1u;
+            bad_image = hdr[0] != CST_IMG_MAGIC || hdr[1] != p.tab_slots || hdr[3] != (u32)p.use_eos;
+            R = bad_image ? 0 : (int)hdr[2];
+        }
         if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
-        if (bad_rows && p.ctl) atomicAdd(&p.ctl[1], bad_rows);
+        if (bad_image && threadIdx.x == 0) ++bad_rows;
+        if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+        if (MODE == CST_MODE_COOK) {
+            // cooking: what phase R left in shared memory (header, ref norms and lengths, table) is the
+            // video's image.  A video with no refs stages an empty table; one with more refs than a
+            // single pass holds cannot be staged and gets an invalid header (scores from it are NaN).
+            uint4* img = reinterpret_cast<uint4*>(hdr);
+            if (R == 0) {
+                for (u32 i = threadIdx.x; i < p.tab_slots + (u32)(CST_IMG_HEAD / 16); i += blockDim.x)
+                    img[i] = make_uint4(0, 0, 0, 0);
+                __syncthreads();
+            }
+            if (threadIdx.x == 0) {
+                hdr[0] = (R <= p.chunk_refs) ? CST_IMG_MAGIC : 0u;
+                hdr[1] = p.tab_slots;
+                hdr[2] = (u32)R;
+                hdr[3] = (u32)p.use_eos;
+            }
+            __syncthreads();
+            uint4* out = reinterpret_cast<uint4*>(p.cook_out + (size_t)video * (size_t)p.cooked_stride);
+            for (u32 i = threadIdx.x; i < p.tab_slots + (u32)(CST_IMG_HEAD / 16); i += blockDim.x) out[i] = img[i];
+            __syncthreads();
+            continue;
+        }
 
         // ---- phase B, spread over the whole CTA (a lone warp would hold 9 idle ones) ----
         // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
         // (1 / R by reciprocal + multiply: a full double division is ~50 instructions of code
         // in a kernel that is sensitive to its instruction footprint; the result differs from
         // the reference's "/ len(refs)" by at most an ulp, the bar is 1e-5)
-        const double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
+        double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
+        if (bad_image) inv_R = __longlong_as_double(0x7ff8000000000000ll);   // not this build's image: NaN, loudly
         for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
             const double s = (sc[c] * 0.25) * inv_R * 10.0;
             sc[c] = s;
@@ -925,16 +1031,37 @@ static void stat_counts(int mode, int64_t n_cand, int seq_per_img, int k, double
     }
 }
 
+// every n-gram instance of the staged refs gets at most one slot (plus, for an n-gram repeated
+// inside a ref, one count slot paid for by the repeat itself); 25 % head-room keeps probes short
+static u32 table_slots_for(int chunk_refs, int ref_width) {
+    const u32 worst = (u32)chunk_refs * (u32)grams_per_row(ref_width);
+    const u32 slots = worst + worst / 4 + 8;
+    return slots < 64 ? 64 : slots;
+}
+
+extern "C" int64_t cst_refs_cooked_bytes(int32_t ref_width, int32_t refs_per_video) {
+    if (ref_width < 1 || ref_width > CST_MAX_ROW_WIDTH || refs_per_video < 1 || refs_per_video > 32) return -1;
+    const int64_t raw = (int64_t)CST_IMG_HEAD + (int64_t)table_slots_for(refs_per_video, ref_width) * (int64_t)sizeof(VidSlot);
+    return (raw + 127) / 128 * 128;
+}
+
 static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st) {
     static thread_local size_t configured[64] = {0};
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || configured[dev] < smem) {
-        CUDA_TRY(cudaFuncSetAttribute(k_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_COOK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (dev < 64) configured[dev] = smem;
     }
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
-    k_score<<<grid, threads, smem, st>>>(p);
+    if (p.cook_out)
+        k_score<CST_MODE_COOK><<<grid, threads, smem, st>>>(p);
+    else if (p.cooked)
+        k_score<CST_MODE_STAGED><<<grid, threads, smem, st>>>(p);
+    else
+        k_score<CST_MODE_RAW><<<grid, threads, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
@@ -946,7 +1073,8 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
                         const int64_t* ref_offsets, int32_t refs_per_video, int64_t n_videos,
                         int32_t cands_per_video, int32_t use_eos, int mode, int scb_k, const double* bcmr,
                         float* reward, double* scores, double* stats, void* scratch, int64_t scratch_bytes,
-                        cudaStream_t st) {
+                        cudaStream_t st, const void* cooked = nullptr, const int64_t* cooked_index = nullptr,
+                        int64_t cooked_stride = 0) {
     if (!t) return fail(CST_E_ARG, "%s: table is NULL", who);
     if (n_cand < 0 || n_videos < 0 || cands_per_video < 1) return fail(CST_E_ARG, "%s: negative size", who);
     if (n_cand != n_videos * (int64_t)cands_per_video)
@@ -964,7 +1092,16 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (n_cand == 0) {
         return CST_OK;
     }
-    if (!cand || !refs) return fail(CST_E_ARG, "%s: NULL rows", who);
+    if (!cand || (!refs && !cooked)) return fail(CST_E_ARG, "%s: NULL rows", who);
+    if (cooked) {
+        if (refs_per_video < 1 || refs_per_video > 32)
+            return fail(CST_E_RANGE, "%s: staged references hold at most 32 refs per video (got %d)", who,
+                        refs_per_video);
+        if (cooked_stride != cst_refs_cooked_bytes(ref_width, refs_per_video))
+            return fail(CST_E_ARG, "%s: image stride %lld does not match ref_width %d / refs_per_video %d", who,
+                        (long long)cooked_stride, ref_width, refs_per_video);
+        if (reinterpret_cast<uintptr_t>(cooked) & 15u) return fail(CST_E_ARG, "%s: images must be 16-byte aligned", who);
+    }
     if (mode == CST_BASE_GREEDY && !greedy) return fail(CST_E_ARG, "%s: greedy rows required", who);
 
     DeviceGuard guard(t->device);
@@ -984,9 +1121,12 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     p.refs = refs;
     p.ref_width = ref_width;
     p.ref_stride = ref_stride;
-    p.ref_offsets = ref_offsets;
+    p.ref_offsets = cooked ? nullptr : ref_offsets;
     p.refs_per_video = refs_per_video;
     p.chunk_refs = refs_per_video < 32 ? (refs_per_video < 1 ? 1 : refs_per_video) : 32;
+    p.cooked = reinterpret_cast<const unsigned char*>(cooked);
+    p.cooked_index = cooked_index;
+    p.cooked_stride = cooked_stride;
     p.n_videos = n_videos;
     p.cands_per_video = cands_per_video;
     p.use_eos = use_eos ? 1 : 0;
@@ -1002,14 +1142,13 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
             return fail(CST_E_ARG, "%s: scratch too small (%lld < %lld bytes)", who, (long long)scratch_bytes,
                         (long long)need);
         p.ctl = reinterpret_cast<u32*>(scratch);   // [1] also collects bad rows in scores-only mode
+        p.bad_out = p.ctl + 1;
         p.partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
         if (mode >= 0) stat_counts(mode, n_cand, cands_per_video, scb_k, p.n_m, p.n_b);
     }
     // every n-gram instance of the staged refs gets at most one slot (plus, for an
     // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
-    const u32 worst = (u32)p.chunk_refs * (u32)grams_per_row(ref_width);
-    p.tab_slots = worst + worst / 4 + 8;
-    if (p.tab_slots < 64) p.tab_slots = 64;
+    p.tab_slots = table_slots_for(p.chunk_refs, ref_width);
 #ifdef CST_EXPERIMENT
     if (const char* e = getenv("CST_EXP_SLOTS")) p.tab_slots = (u32)atoi(e);
 #endif
@@ -1077,6 +1216,37 @@ extern "C" int cst_scb_apply(const double* scores, const double* other, int64_t 
     return CST_OK;
 }
 
+static int reward_impl(const char* who, const cst_df_table* table, const void* cand, const void* greedy,
+                       int32_t cand_dtype, int64_t n_cand, int32_t cand_width, int64_t cand_stride, const void* refs,
+                       int32_t ref_dtype, int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
+                       int32_t refs_per_video, int64_t n_videos, int32_t cands_per_video, int32_t use_eos,
+                       int32_t mode, int32_t seq_per_img, int32_t scb_k, const double* bcmrscores, float* reward_out,
+                       double* scores_out, double* stats_out, void* scratch, int64_t scratch_bytes, void* stream,
+                       const void* cooked, const int64_t* cooked_index, int64_t cooked_stride) {
+    int rc = check_baseline_args(who, mode, seq_per_img, scb_k, bcmrscores);
+    if (rc != CST_OK) return rc;
+    if (n_cand > 0 && (!reward_out || !stats_out)) return fail(CST_E_ARG, "%s: NULL output", who);
+    if (n_cand % seq_per_img != 0)
+        return fail(CST_E_ARG, "%s: n_cand %lld is not a multiple of seq_per_img %d", who, (long long)n_cand,
+                    seq_per_img);
+    if (cands_per_video == seq_per_img) {
+        return score_common(who, table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs,
+                            ref_dtype, ref_width, ref_stride, ref_offsets, refs_per_video, n_videos,
+                            cands_per_video, use_eos, mode, scb_k, bcmrscores, reward_out, scores_out, stats_out,
+                            scratch, scratch_bytes, (cudaStream_t)stream, cooked, cooked_index, cooked_stride);
+    }
+    // baseline rows do not coincide with videos (expand_feat == 0): score, then baseline
+    if (!scores_out) return fail(CST_E_ARG, "%s: scores_out is required when cands_per_video != seq_per_img", who);
+    rc = score_common(who, table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
+                      ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, -1, 0,
+                      nullptr, nullptr, scores_out, nullptr, scratch, scratch_bytes, (cudaStream_t)stream, cooked,
+                      cooked_index, cooked_stride);
+    if (rc != CST_OK) return rc;
+    const double* other = (mode == CST_BASE_GREEDY) ? scores_out + n_cand : bcmrscores;
+    return cst_scb_apply(scores_out, other, n_cand / seq_per_img, seq_per_img, mode, scb_k, reward_out, stats_out,
+                         scratch, scratch_bytes, table->device, stream);
+}
+
 extern "C" int cst_reward(const cst_df_table* table, const void* cand, const void* greedy, int32_t cand_dtype,
                           int64_t n_cand, int32_t cand_width, int64_t cand_stride, const void* refs,
                           int32_t ref_dtype, int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
@@ -1084,27 +1254,81 @@ extern "C" int cst_reward(const cst_df_table* table, const void* cand, const voi
                           int32_t mode, int32_t seq_per_img, int32_t scb_k, const double* bcmrscores,
                           float* reward_out, double* scores_out, double* stats_out, void* scratch,
                           int64_t scratch_bytes, void* stream) {
-    int rc = check_baseline_args("cst_reward", mode, seq_per_img, scb_k, bcmrscores);
-    if (rc != CST_OK) return rc;
-    if (n_cand > 0 && (!reward_out || !stats_out)) return fail(CST_E_ARG, "cst_reward: NULL output");
-    if (n_cand % seq_per_img != 0)
-        return fail(CST_E_ARG, "cst_reward: n_cand %lld is not a multiple of seq_per_img %d", (long long)n_cand,
-                    seq_per_img);
-    if (cands_per_video == seq_per_img) {
-        return score_common("cst_reward", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs,
-                            ref_dtype, ref_width, ref_stride, ref_offsets, refs_per_video, n_videos,
-                            cands_per_video, use_eos, mode, scb_k, bcmrscores, reward_out, scores_out, stats_out,
-                            scratch, scratch_bytes, (cudaStream_t)stream);
-    }
-    // baseline rows do not coincide with videos (expand_feat == 0): score, then baseline
-    if (!scores_out) return fail(CST_E_ARG, "cst_reward: scores_out is required when cands_per_video != seq_per_img");
-    rc = score_common("cst_reward", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
-                      ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, -1, 0,
-                      nullptr, nullptr, scores_out, nullptr, scratch, scratch_bytes, (cudaStream_t)stream);
-    if (rc != CST_OK) return rc;
-    const double* other = (mode == CST_BASE_GREEDY) ? scores_out + n_cand : bcmrscores;
-    return cst_scb_apply(scores_out, other, n_cand / seq_per_img, seq_per_img, mode, scb_k, reward_out, stats_out,
-                         scratch, scratch_bytes, table->device, stream);
+    return reward_impl("cst_reward", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
+                       ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, mode,
+                       seq_per_img, scb_k, bcmrscores, reward_out, scores_out, stats_out, scratch, scratch_bytes,
+                       stream, nullptr, nullptr, 0);
+}
+
+extern "C" int cst_reward_cooked(const cst_df_table* table, const void* cand, const void* greedy, int32_t cand_dtype,
+                                 int64_t n_cand, int32_t cand_width, int64_t cand_stride, const void* images,
+                                 int64_t image_stride, const int64_t* image_index, int32_t ref_width,
+                                 int32_t refs_per_video, int64_t n_videos, int32_t cands_per_video, int32_t use_eos,
+                                 int32_t mode, int32_t seq_per_img, int32_t scb_k, const double* bcmrscores,
+                                 float* reward_out, double* scores_out, double* stats_out, void* scratch,
+                                 int64_t scratch_bytes, void* stream) {
+    if (n_cand > 0 && !images) return fail(CST_E_ARG, "cst_reward_cooked: images is NULL");
+    return reward_impl("cst_reward_cooked", table, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, nullptr,
+                       CST_DTYPE_I32, ref_width, ref_width, nullptr, refs_per_video, n_videos, cands_per_video,
+                       use_eos, mode, seq_per_img, scb_k, bcmrscores, reward_out, scores_out, stats_out, scratch,
+                       scratch_bytes, stream, images, image_index, image_stride);
+}
+
+// Phase R of k_score run once per video and kept: one image per video at images_out + v * image_stride
+// (cst_refs_cooked_bytes).  bad_rows_out (device, optional) receives the number of reference rows that
+// held ids outside [-1, 65534], plus one per video with more than refs_per_video refs (its image is
+// marked invalid).
+extern "C" int cst_refs_cook(const cst_df_table* t, const void* refs, int32_t ref_dtype, int64_t n_rows,
+                             int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
+                             int32_t refs_per_video, int64_t n_videos, int32_t use_eos, void* images_out,
+                             int64_t image_stride, uint32_t* bad_rows_out, void* stream) {
+    const char* who = "cst_refs_cook";
+    if (!t) return fail(CST_E_ARG, "%s: table is NULL", who);
+    if (n_videos < 0 || n_rows < 0) return fail(CST_E_ARG, "%s: negative size", who);
+    if (ref_width < 1 || ref_width > CST_MAX_ROW_WIDTH)
+        return fail(CST_E_RANGE, "%s: row width %d outside [1, %d]", who, ref_width, CST_MAX_ROW_WIDTH);
+    if (ref_stride < ref_width) return fail(CST_E_ARG, "%s: stride < width", who);
+    if (!dtype_bytes(ref_dtype)) return fail(CST_E_ARG, "%s: bad dtype", who);
+    if (refs_per_video < 1 || refs_per_video > 32)
+        return fail(CST_E_RANGE, "%s: at most 32 refs per video can be staged (got %d)", who, refs_per_video);
+    if (!ref_offsets && n_rows != n_videos * (int64_t)refs_per_video)
+        return fail(CST_E_ARG, "%s: n_rows (%lld) != n_videos (%lld) * refs_per_video (%d)", who, (long long)n_rows,
+                    (long long)n_videos, refs_per_video);
+    if (image_stride != cst_refs_cooked_bytes(ref_width, refs_per_video))
+        return fail(CST_E_ARG, "%s: image stride %lld, expected %lld", who, (long long)image_stride,
+                    (long long)cst_refs_cooked_bytes(ref_width, refs_per_video));
+    if (n_videos == 0) return CST_OK;
+    if (!refs || !images_out) return fail(CST_E_ARG, "%s: NULL argument", who);
+    if (reinterpret_cast<uintptr_t>(images_out) & 15u) return fail(CST_E_ARG, "%s: images must be 16-byte aligned", who);
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "%s: cannot select device %d", who, t->device);
+
+    ScoreParams p;
+    memset(&p, 0, sizeof(p));
+    p.df = view_of(t);
+    p.gauss = t->gauss;
+    p.refs = refs;
+    p.ref_esz = dtype_bytes(ref_dtype);
+    p.cand_esz = p.ref_esz;
+    p.ref_width = ref_width;
+    p.cand_width = 1;
+    p.ref_stride = ref_stride;
+    p.ref_offsets = ref_offsets;
+    p.refs_per_video = refs_per_video;
+    p.chunk_refs = refs_per_video;
+    p.n_videos = n_videos;
+    p.cands_per_video = 0;
+    p.use_eos = use_eos ? 1 : 0;
+    p.mode = -1;
+    p.bad_out = bad_rows_out;
+    p.tab_slots = table_slots_for(p.chunk_refs, ref_width);
+    p.cook_out = reinterpret_cast<unsigned char*>(images_out);
+    p.cooked_stride = image_stride;
+    int nwarps = (refs_per_video + 1) / 2;
+    if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
+    if (nwarps < 4) nwarps = 4;
+    const size_t smem = CST_SCORE_FIXED_SMEM + (size_t)p.tab_slots * sizeof(VidSlot);
+    return launch_score(p, nwarps * 32, smem, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------

@@ -69,7 +69,7 @@ class RefSet:
 
     @classmethod
     def coerce(cls, data_gts, device):
-        if isinstance(data_gts, cls):
+        if isinstance(data_gts, (cls, CookedRefs)):
             return data_gts
         if torch.is_tensor(data_gts):
             if data_gts.dim() != 3:
@@ -108,6 +108,61 @@ class RefStore:
         if len(counts) and np.all(counts == counts[0]):
             return RefSet(picked, per_video=int(counts[0]))
         return RefSet(picked, offsets=offsets)
+
+
+class CookedRefs:
+    """References staged once: the reference-side half of the scoring
+    kernel -- canonicalisation, n-gram table with presence masks, norms, lengths -- is run one
+    time per video by ``cst_refs_cook`` and its result kept in device memory, one image per
+    video.  The ground-truth captions never change during training, yet the reference cooks
+    them again on every call (``cook_refs`` under ``utils.py:208,274``).
+
+    ``CookedRefs.cook(refs, scorer, use_eos)`` builds the images from a :class:`RefSet` /
+    ``(V, R, W)`` tensor / list of arrays; ``cooked.batch(video_ids)`` selects a step's videos
+    (only the indices move); the result is accepted wherever ``data_gts`` is.  Images are
+    tied to the scorer's df table and to ``use_eos``; at most 32 refs per video.
+    """
+
+    def __init__(self, images, stride, ref_width, max_refs, use_eos, table, index=None, n_videos=None,
+                 bad_rows=None):
+        self.images, self.stride = images, int(stride)
+        self.ref_width, self.max_refs, self.use_eos = int(ref_width), int(max_refs), int(bool(use_eos))
+        self.table = table
+        self.index = index
+        self.n_videos = int(n_videos if n_videos is not None else images.shape[0])
+        self.bad_rows = bad_rows            # device uint32[1]: out-of-range ref rows + invalid images
+
+    @classmethod
+    def cook(cls, data_gts, scorer, use_eos=0):
+        table = scorer.table
+        dev = table.device
+        refs = RefSet.coerce(data_gts, dev)
+        if refs.max_refs > 32:
+            raise ValueError('at most 32 refs per video can be staged (got %d)' % refs.max_refs)
+        w = refs.rows.shape[1]
+        max_refs = max(refs.max_refs, 1)
+        stride = int(lib.cst_refs_cooked_bytes(w, max_refs))
+        if stride < 0:
+            raise ValueError('rows of width %d / %d refs per video cannot be staged' % (w, max_refs))
+        images = torch.empty((refs.n_videos, stride), dtype=torch.uint8, device=dev)
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        check(lib.cst_refs_cook(table.handle, refs.rows.data_ptr(), _row_dtype(refs.rows), refs.rows.shape[0], w,
+                                refs.rows.stride(0), refs.offsets.data_ptr() if refs.offsets is not None else None,
+                                max_refs, refs.n_videos, int(use_eos), images.data_ptr(), stride, bad.data_ptr(),
+                                _stream(dev)))
+        return cls(images, stride, w, max_refs, use_eos, table, bad_rows=bad)
+
+    def batch(self, video_ids):
+        """The step's videos, in order: only the int64 indices go to the device."""
+        if torch.is_tensor(video_ids):
+            idx = video_ids.to(self.images.device, torch.int64).contiguous()
+        else:
+            idx = torch.from_numpy(np.ascontiguousarray(video_ids, dtype=np.int64)).to(self.images.device)
+        return CookedRefs(self.images, self.stride, self.ref_width, self.max_refs, self.use_eos, self.table,
+                          index=idx, n_videos=idx.numel(), bad_rows=self.bad_rows)
+
+    def nbytes(self):
+        return self.images.numel()
 
 
 def _narrow(rows):
@@ -168,6 +223,18 @@ def _launch_reward(scorer, sampled, greedy, refs, cands_per_video, use_eos, mode
     if want_scores or not fused:
         scores = torch.empty(n * (2 if greedy is not None else 1), dtype=torch.float64, device=dev)
     scratch = _scratch_for(dev, max(n_videos, n // seq_per_img))
+    if isinstance(refs, CookedRefs):
+        if refs.table is not scorer.table or refs.use_eos != int(bool(use_eos)):
+            raise ValueError('these references were staged for another df table or use_eos')
+        check(lib.cst_reward_cooked(
+            scorer.table.handle, sampled.data_ptr(), greedy.data_ptr() if greedy is not None else None,
+            _row_dtype(sampled), n, sampled.shape[1], sampled.stride(0),
+            refs.images.data_ptr(), refs.stride, refs.index.data_ptr() if refs.index is not None else None,
+            refs.ref_width, refs.max_refs, n_videos, cands_per_video, int(use_eos), mode, seq_per_img, k,
+            bcmr.data_ptr() if bcmr is not None else None,
+            reward.data_ptr(), scores.data_ptr() if scores is not None else None, stats.data_ptr(),
+            scratch.data_ptr(), scratch.numel(), _stream(dev)))
+        return reward, stats, scores
     check(lib.cst_reward(
         scorer.table.handle, sampled.data_ptr(), greedy.data_ptr() if greedy is not None else None,
         _row_dtype(sampled), n, sampled.shape[1], sampled.stride(0),

@@ -234,6 +234,41 @@ int cst_reward_noalloc(const cst_df_table* table,
                        float* reward_out, double* scores_out, double* stats_out,
                        void* stream);
 
+/* ---- staged references (the producer side) -----------------------------
+ * The reference rebuilds every video's reference vectors on every call (cook_refs inside the
+ * scorer's cook_append, reached from utils.py:208,274 with the gts of dataloader.py:138-139),
+ * although the ground-truth captions never change during training.  cst_refs_cook runs that
+ * half of the scoring kernel ONCE per video and keeps the result in device memory -- the
+ * per-video n-gram table with its presence masks, the refs' inverse norms and lengths: one
+ * image of cst_refs_cooked_bytes() per video, about 46 KB for 20 refs of width 30 (MSR-VTT's
+ * 10 k videos: 0.47 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
+ * images of the videos named by image_index (device int64, one per video of the batch; NULL =
+ * images 0..n_videos-1 in order): a step passes video indices instead of reference rows.
+ * Images depend on the df table, use_eos, ref_width and refs_per_video they were cooked with;
+ * an image of another layout, table geometry or use_eos makes the rewards of that video NaN
+ * and is counted in stats_out[4].  At most 32 refs per video (a video with more gets an
+ * invalid image).  bad_rows_out (device, optional, caller zeroes it): += reference rows that
+ * held ids outside [-1, 65534], += 1 per invalid image. */
+int64_t cst_refs_cooked_bytes(int32_t ref_width, int32_t refs_per_video);   /* -1: out of range */
+int cst_refs_cook(const cst_df_table* table,
+                  const void* refs, int32_t ref_dtype, int64_t n_rows, int32_t ref_width,
+                  int64_t ref_stride, const int64_t* ref_offsets /* NULL: uniform */,
+                  int32_t refs_per_video /* exact, or the maximum with ref_offsets */,
+                  int64_t n_videos, int32_t use_eos,
+                  void* images_out, int64_t image_stride, uint32_t* bad_rows_out,
+                  void* stream);
+/* cst_reward with the refs given as images; every other argument as in cst_reward. */
+int cst_reward_cooked(const cst_df_table* table,
+                      const void* cand, const void* greedy, int32_t cand_dtype,
+                      int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                      const void* images, int64_t image_stride, const int64_t* image_index,
+                      int32_t ref_width, int32_t refs_per_video, int64_t n_videos,
+                      int32_t cands_per_video, int32_t use_eos,
+                      int32_t mode, int32_t seq_per_img, int32_t scb_k,
+                      const double* bcmrscores,
+                      float* reward_out, double* scores_out, double* stats_out,
+                      void* scratch, int64_t scratch_bytes, void* stream);
+
 /* Baseline alone on given scores: utils.py:286-288 (WXE: scores are the
  * precomputed consensus scores) and utils.py:292-322.  scores [dev] float64
  * (n_rows, seq_per_img); for CST_BASE_GREEDY `other` holds the greedy scores, for

@@ -50,6 +50,15 @@ for case in range(n_cases):
     per = RefSet.coerce(r.repeat_interleave(s, dim=0)[:min(64, n_videos * s)], dev)
     bsc = scorer.score_rows(c[:per.n_videos], per, 1, use_eos=ue)
     assert torch.equal(a[:per.n_videos], bsc), 'fused vs per-candidate mismatch in case %d' % case
+    if n_refs <= 32:                 # references staged once give the bits of the raw rows
+        cooked = cst.CookedRefs.cook(r, scorer, use_eos=ue)
+        ids = torch.from_numpy(rng.permutation(n_videos)).to(dev)
+        rew2, _, _, st2 = cst.get_cst_reward(c.reshape(n_videos, s, cw)[ids].reshape(-1, cw), cooked.batch(ids), scorer,
+                                             expand_feat=1, seq_per_img=s, scb_captions=k, scb_baseline=2,
+                                             use_eos=ue, return_stats=True)
+        want = outs[0][0].reshape(n_videos, s)[ids].reshape(-1)
+        assert torch.equal(rew2[:, 0], want), 'staged vs raw mismatch in case %d' % case
+        del cooked
     g2 = torch.roll(c, 1, 0)
     cst.get_self_critical_reward(c, g2, r, scorer, expand_feat=1, seq_per_img=s, use_eos=ue)
 torch.cuda.synchronize()
