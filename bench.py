@@ -346,7 +346,21 @@ def product_arm(args):
                   'images_bytes_total': cooked.nbytes(),
                   'same_bits_as_raw_rows': bool(torch.equal(rew_c, rew)),
                   'note': 'cst_refs_cook once outside the timed region, then cst_reward_cooked per step'}
-        del cooked, cooked_b
+        # ... and end to end: pinned host candidates in, pinned rewards out, refs already staged
+        pipe_s = cst.HostRewardPipeline(scorer, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1,
+                                        slices=args.e2e_slices)
+        out_s = torch.empty(n_cap, dtype=torch.float32).pin_memory()
+        for i in range(1 + max(3, min(args.steps, 10))):
+            if i == 1:
+                barrier()
+                t0 = time.perf_counter()
+            pipe_s(h_cand, cooked_b, out=out_s)
+            torch.cuda.synchronize()
+        e2e_staged_s = (time.perf_counter() - t0) / max(3, min(args.steps, 10))
+        staged['e2e'] = {'value': n_cap / e2e_staged_s, 'unit': UNIT + ' per GPU', 'ms_per_step': 1e3 * e2e_staged_s,
+                         'h2d_bytes_per_step': int(h_cand.numel() * 4), 'd2h_bytes_per_step': int(out_s.numel() * 4),
+                         'same_bits_as_raw_rows': bool(torch.equal(out_s.to(dev), rew[:, 0]))}
+        del cooked, cooked_b, pipe_s
 
     # ---- end to end through the public API with HOST buffers -----------------------
     e2e_steps = max(3, min(args.steps, 10))

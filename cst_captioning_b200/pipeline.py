@@ -14,14 +14,15 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .reward import RefSet, get_cst_reward
+from .reward import CookedRefs, RefSet, get_cst_reward
 
 
 class HostRewardPipeline:
     """``get_cst_reward`` over pinned host tensors with copy/compute overlap.
 
     ``sampled``: pinned int tensor ``(videos * seq_per_img, T)``; ``refs``: pinned int
-    tensor ``(videos, R, W)``; optional ``bcmrscores`` pinned float64
+    tensor ``(videos, R, W)`` -- or a :class:`CookedRefs` batch (references staged once on
+    the device: only the candidates are uploaded); optional ``bcmrscores`` pinned float64
     ``(videos, seq_per_img)``.  Keyword arguments are those of ``get_cst_reward``
     (``utils.py:229-238``) with ``expand_feat=1`` implied.
     """
@@ -39,12 +40,15 @@ class HostRewardPipeline:
         self._bufs = None
 
     def _buffers(self, sampled, refs, bcmr, per):
-        key = (per, sampled.shape[1], sampled.dtype, tuple(refs.shape[1:]), refs.dtype, bcmr is not None)
+        staged = isinstance(refs, CookedRefs)
+        key = (per, sampled.shape[1], sampled.dtype, None if staged else tuple(refs.shape[1:]),
+               None if staged else refs.dtype, bcmr is not None)
         if self._bufs is None or self._bufs[0] != key:
             def mk():
                 return {'cand': torch.empty((per * self.seq_per_img, sampled.shape[1]), dtype=sampled.dtype,
                                             device=self.device),
-                        'refs': torch.empty((per,) + tuple(refs.shape[1:]), dtype=refs.dtype, device=self.device),
+                        'refs': None if staged else torch.empty((per,) + tuple(refs.shape[1:]), dtype=refs.dtype,
+                                                                device=self.device),
                         'bcmr': torch.empty((per, self.seq_per_img), dtype=torch.float64, device=self.device)
                         if bcmr is not None else None,
                         'uploaded': torch.cuda.Event(), 'consumed': torch.cuda.Event(), 'used': False}
@@ -56,7 +60,10 @@ class HostRewardPipeline:
         The caller synchronises (``torch.cuda.synchronize()`` or the returned tensors'
         streams) before reading ``out``."""
         s = self.seq_per_img
-        n_videos = refs.shape[0]
+        staged = isinstance(refs, CookedRefs)
+        n_videos = refs.n_videos if staged else refs.shape[0]
+        if staged:
+            index = refs.index if refs.index is not None else torch.arange(n_videos, device=self.device)
         if sampled.shape[0] != n_videos * s:
             raise ValueError('sampled must hold seq_per_img rows per video')
         if out is None:
@@ -74,9 +81,12 @@ class HostRewardPipeline:
                 if b['used']:
                     self.copy_stream.wait_event(b['consumed'])      # the slice two back has been scored
                 cand = b['cand'][:(hi - lo) * s]
-                rr = b['refs'][:hi - lo]
                 cand.copy_(sampled[lo * s:hi * s], non_blocking=True)
-                rr.copy_(refs[lo:hi], non_blocking=True)
+                if staged:
+                    rr = refs.batch(index[lo:hi])
+                else:
+                    rr = b['refs'][:hi - lo]
+                    rr.copy_(refs[lo:hi], non_blocking=True)
                 bc = None
                 if bcmrscores is not None:
                     bc = b['bcmr'][:hi - lo]
