@@ -5,7 +5,7 @@ only on its own candidates and references plus the global df table, and the SCB
 baselines are per video (``utils.py:308-315``), so the batch shards by video with no
 data-path exchange: rank g scores a contiguous slice, the df table is replicated, and
 the only thing ranks share is the pair of logged means (``train.py:229-233``), i.e. an
-all-reduce of the five statistics sums the kernel writes.
+all-reduce of the statistics sums the kernel writes.
 
 One process per GPU (``torchrun``); NCCL on the GPUs, gloo in the CPU tests.
 """

@@ -164,6 +164,18 @@ class CookedRefs:
     def nbytes(self):
         return self.images.numel()
 
+    def __len__(self):
+        return self.n_videos
+
+    def __getitem__(self, videos):
+        """A slice of this batch's videos (what ``dist.shard_batch`` takes of ``data_gts``)."""
+        if not isinstance(videos, slice):
+            raise TypeError('CookedRefs supports slices; use batch(ids) for arbitrary videos')
+        lo, hi, step = videos.indices(self.n_videos)
+        if self.index is not None:
+            return self.batch(self.index[lo:hi:step])
+        return self.batch(torch.arange(lo, hi, step, device=self.images.device))
+
 
 def _narrow(rows):
     """Host int64 rows -> int32 when every id fits (halves the upload; ids outside
