@@ -90,6 +90,9 @@ static DfView view_of(const cst_df_table* t) {
 
 static u32 df_buckets_for(int64_t n) {
     int64_t nb = (2 * n + CST_BUCKET - 1) / CST_BUCKET + 4;   // load factor <= 0.5
+#ifdef CST_EXPERIMENT
+    if (const char* e = getenv("CST_EXP_LOAD_PCT")) nb = (100 * n / atoi(e) + CST_BUCKET - 1) / CST_BUCKET + 4;
+#endif
     if (nb < 256) nb = 256;
     return (u32)nb;
 }
