@@ -20,6 +20,7 @@
 #include <atomic>
 #include <mutex>
 #include <new>
+#include <utility>
 #include <vector>
 
 #include "cst_common.cuh"
@@ -200,9 +201,11 @@ extern "C" int cst_df_create(const uint64_t* keys, const double* df, int64_t n, 
     const size_t slots = (size_t)nb * CST_BUCKET;
     std::vector<u64> h_keys;
     std::vector<u32> h_dfc;
+    std::vector<unsigned char> h_over;        // bucket b was full when an insertion came by
     try {
         h_keys.assign(slots, 0ull);
         h_dfc.assign(slots, 0u);
+        h_over.assign(nb, 0);
     } catch (const std::bad_alloc&) {
         return fail(CST_E_NOMEM, "cst_df_create: out of host memory for %zu slots", slots);
     }
@@ -226,7 +229,17 @@ extern "C" int cst_df_create(const uint64_t* keys, const double* df, int64_t n, 
                 h_dfc[(size_t)b * CST_BUCKET + j] = (u32)d;
                 break;
             }
+            h_over[b] = 1;
             b = (b + 1 == nb) ? 0u : b + 1;
+        }
+    }
+    // the overflow mark of a full bucket: the order of its first two keys (bucket_resolve)
+    for (u32 b = 0; b < nb; ++b) {
+        u64* k = &h_keys[(size_t)b * CST_BUCKET];
+        if (k[CST_BUCKET - 1] == 0ull) continue;
+        if ((k[0] > k[1]) != (h_over[b] != 0)) {
+            std::swap(k[0], k[1]);
+            std::swap(h_dfc[(size_t)b * CST_BUCKET], h_dfc[(size_t)b * CST_BUCKET + 1]);
         }
     }
     cst_df_table* t = nullptr;
@@ -747,7 +760,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(cons
 #pragma unroll
                         for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
                         double idf[4];
-                        df_probe4(p.df, key, h, lead, idf);
+                        df_probe4<MODE != CST_MODE_RAW>(p.df, key, h, lead, idf);
                         double n2[4];
 #pragma unroll
                         for (int k = 0; k < 4; ++k) {
@@ -1405,7 +1418,7 @@ __global__ void __launch_bounds__(256) k_df_build(const void* __restrict__ rows,
 // Move the counted keys into the final bucketed table.  Slots of a bucket fill front
 // to back (the lookup relies on it: an empty last slot ends a probe).
 __global__ void k_df_rehash(const u64* __restrict__ g_keys, const u32* __restrict__ g_cnt, u32 g_cap, u64* keys,
-                            u32* dfc, u32 n_buckets) {
+                            u32* dfc, u32 n_buckets, unsigned long long* over /* [n_buckets * 4], zeroed */) {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g_cap) return;
     const u64 key = g_keys[i];
@@ -1419,7 +1432,25 @@ __global__ void k_df_rehash(const u64* __restrict__ g_keys, const u32* __restric
                 return;
             }
         }
+        over[(size_t)b * CST_BUCKET] = 1ull;      // full when this key came by (every writer stores the same)
         b = (b + 1 == n_buckets) ? 0u : b + 1;
+    }
+}
+
+// The overflow mark of a full bucket is the order of its first two keys (bucket_resolve).
+__global__ void k_df_order(u64* keys, u32* dfc, const unsigned long long* __restrict__ over, u32 n_buckets) {
+    const u32 b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_buckets) return;
+    u64* k = keys + (size_t)b * CST_BUCKET;
+    if (k[CST_BUCKET - 1] == 0ull) return;
+    const u64 k0 = k[0], k1 = k[1];
+    if ((k0 > k1) != (over[(size_t)b * CST_BUCKET] != 0ull)) {
+        u32* d = dfc + (size_t)b * CST_BUCKET;
+        const u32 d0 = d[0];
+        k[0] = k1;
+        k[1] = k0;
+        d[0] = d[1];
+        d[1] = d0;
     }
 }
 
@@ -1502,7 +1533,14 @@ extern "C" int cst_df_build_from_rows(const void* rows, int32_t dtype, int64_t n
     }
     rc = table_alloc(device, df_buckets_for((int64_t)h_counters[0]), idf_by_df, n_videos, &t);
     if (rc != CST_OK) goto done;
-    k_df_rehash<<<(g_cap + 255) / 256, 256>>>(g_keys, g_cnt, g_cap, t->keys, t->dfc, t->n_buckets);
+    // the idf array is filled last (table_finish): until then it holds the overflow marks
+    BUILD_TRY(cudaMemset(t->idfv, 0, (size_t)t->n_buckets * CST_BUCKET * sizeof(double)));
+    k_df_rehash<<<(g_cap + 255) / 256, 256>>>(g_keys, g_cnt, g_cap, t->keys, t->dfc, t->n_buckets,
+                                              reinterpret_cast<unsigned long long*>(t->idfv));
+    COUNT_LAUNCH();
+    BUILD_TRY(cudaGetLastError());
+    k_df_order<<<(t->n_buckets + 255) / 256, 256>>>(t->keys, t->dfc, reinterpret_cast<const unsigned long long*>(t->idfv),
+                                                    t->n_buckets);
     COUNT_LAUNCH();
     BUILD_TRY(cudaGetLastError());
     BUILD_TRY(cudaDeviceSynchronize());
