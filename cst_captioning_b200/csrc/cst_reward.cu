@@ -589,8 +589,12 @@ static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_IMG_HEAD % 16 == 0, "the imag
 #define CST_MODE_RAW 0      /* phase R from the reference rows, phase C, phase B */
 #define CST_MODE_STAGED 1   /* phase R replaced by the copy of the video's image (cst_refs_cook) */
 #define CST_MODE_COOK 2     /* phase R only; its result is written out as the video's image */
-template <int MODE>
-__global__ void __launch_bounds__(CST_MAX_WARPS * 32, CST_MIN_CTAS) k_score(const ScoreParams p) {
+// CTAS: resident CTAs per SM the register allocation is held to.  CST_MIN_CTAS (4: 48 registers) is
+// the throughput build; 2 (90 registers, no spills) finishes a lone video 15 % sooner and serves
+// batches small enough that two CTAs per SM hold them all (BASELINE configs 1 and 3: 64 videos).
+#define CST_SMALL_BATCH_CTAS 2
+template <int MODE, int CTAS>
+__global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
     __shared__ int s_ticket[2];                      // next item of the phase's work list
@@ -1070,18 +1074,32 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || configured[dev] < smem) {
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_COOK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, CST_MIN_CTAS>, attr, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, CST_MIN_CTAS>, attr, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_COOK, CST_MIN_CTAS>, attr, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS>, attr, (int)smem));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS>, attr, (int)smem));
         if (dev < 64) configured[dev] = smem;
     }
+    static thread_local int n_sm[64] = {0};
+    int sms = 148;
+    if (dev < 64) {
+        if (!n_sm[dev]) CUDA_TRY(cudaDeviceGetAttribute(&n_sm[dev], cudaDevAttrMultiProcessorCount, dev));
+        sms = n_sm[dev];
+    }
+    const bool small = p.n_videos <= (int64_t)CST_SMALL_BATCH_CTAS * sms;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
     if (p.cook_out)
-        k_score<CST_MODE_COOK><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_COOK, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
+    else if (p.cooked && small)
+        k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS><<<grid, threads, smem, st>>>(p);
     else if (p.cooked)
-        k_score<CST_MODE_STAGED><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_STAGED, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
+    else if (small)
+        k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS><<<grid, threads, smem, st>>>(p);
     else
-        k_score<CST_MODE_RAW><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_RAW, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
