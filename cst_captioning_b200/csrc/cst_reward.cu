@@ -917,6 +917,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
                 __syncthreads();
             }
             if (threadIdx.x == 0) {
+                if (R > p.chunk_refs && p.bad_out) atomicAdd(p.bad_out, 1u);
                 hdr[0] = (R <= p.chunk_refs) ? CST_IMG_MAGIC : 0u;
                 hdr[1] = p.tab_slots;
                 hdr[2] = (u32)R;
