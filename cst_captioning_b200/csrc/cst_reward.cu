@@ -593,8 +593,16 @@ static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_IMG_HEAD % 16 == 0, "the imag
 // the throughput build; 2 (90 registers, no spills) finishes a lone video 15 % sooner and serves
 // batches small enough that two CTAs per SM hold them all (BASELINE configs 1 and 3: 64 videos).
 #define CST_SMALL_BATCH_CTAS 2
-template <int MODE, int CTAS>
+// BASE: the baseline a launch is specialised for (CST_BASE_GREEDY / SCB_GT / SCB_SAMPLE, with no scores
+// output and uniform ref counts -- the three shapes of a training step), or CST_BASE_ANY: everything
+// decided at run time.  Worth 9 % of the raw-row kernel's instructions and 3 % of its time.
+#define CST_BASE_ANY (-2)
+template <int MODE, int CTAS, int BASE>
 __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreParams p) {
+    const int k_mode = (BASE == CST_BASE_ANY) ? p.mode : BASE;
+    const void* const k_greedy = (BASE == CST_BASE_ANY || BASE == CST_BASE_GREEDY) ? p.greedy : nullptr;
+    double* const k_scores = (BASE == CST_BASE_ANY) ? p.scores : nullptr;
+    const int64_t* const k_offsets = (BASE == CST_BASE_ANY) ? p.ref_offsets : nullptr;
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
     __shared__ int s_ticket[2];                      // next item of the phase's work list
@@ -605,7 +613,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
-    const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
+    const int n_local = p.cands_per_video * ((BASE == CST_BASE_GREEDY || k_greedy) ? 2 : 1);
 
     // Fixed-size arrays first, then the table, then the arrays sized by the candidate count: what the
     // item loop touches sits at compile-time offsets (the address arithmetic folds into the
@@ -643,9 +651,9 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
 #define CST_TICK(i)
 #endif
         int64_t r0, r1;
-        if (p.ref_offsets) {
-            r0 = p.ref_offsets[video];
-            r1 = p.ref_offsets[video + 1];
+        if (k_offsets) {
+            r0 = k_offsets[video];
+            r1 = k_offsets[video + 1];
         } else {
             r0 = video * p.refs_per_video;
             r1 = r0 + p.refs_per_video;
@@ -738,7 +746,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
                             const int64_t ci = video * p.cands_per_video + (gq ? ri - p.cands_per_video : ri);
                             esz = p.cand_esz;
                             width = p.cand_width;
-                            row = reinterpret_cast<const char*>(gq ? p.greedy : p.cand) +
+                            row = reinterpret_cast<const char*>(gq ? k_greedy : p.cand) +
                                   (size_t)ci * (size_t)p.cand_stride * (size_t)esz;
                         }
                         if (!act) width = 0;                         // idle half of an odd pair
@@ -940,17 +948,17 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
         for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
             const double s = (sc[c] * 0.25) * inv_R * 10.0;
             sc[c] = s;
-            if (p.scores) {
+            if (k_scores) {
                 const bool is_greedy = c >= p.cands_per_video;
                 const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
-                p.scores[(is_greedy ? p.n_cand : 0) + ci] = s;
+                k_scores[(is_greedy ? p.n_cand : 0) + ci] = s;
             }
         }
         __syncthreads();
-        if (p.mode >= 0) {
+        if (k_mode >= 0) {
             const int S = p.cands_per_video;
-            const bool scb = (p.mode == CST_BASE_SCB_GT || p.mode == CST_BASE_SCB_SAMPLE);
-            const double* x = (p.mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
+            const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
+            const double* x = (k_mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
             if (scb) {
                 // k lowest of the row (utils.py:294-312): element i is ranked by one warp with
                 // ballots (ties by index = stable sort); low[i] = x_i if its rank < k
@@ -973,19 +981,19 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
             }
             const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
             for (int i = threadIdx.x; i < S; i += blockDim.x) {
-                const double r = (p.mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
+                const double r = (k_mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
                 p.reward[video * S + i] = (float)r;
             }
             if (warp == 0) {                                      // the video's share of the statistics
                 double am = 0.0, ab = 0.0;
                 for (int i = lane; i < S; i += 32) {
                     am += sc[i];
-                    if (p.mode == CST_BASE_GREEDY) ab += sc[S + i];
-                    if (p.mode == CST_BASE_SCB_GT) ab += x[i];
+                    if (k_mode == CST_BASE_GREEDY) ab += sc[S + i];
+                    if (k_mode == CST_BASE_SCB_GT) ab += x[i];
                 }
                 am = warp_sum(am);
                 ab = warp_sum(ab);
-                if (p.mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
+                if (k_mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
                 if (lane == 0) {
                     p.partials[2 * video] = am;
                     p.partials[2 * video + 1] = ab;
@@ -1005,7 +1013,7 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
         }
 #endif
     }
-    if (p.mode >= 0) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
+    if (k_mode >= 0) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
 }
 
 // Standalone baseline over (n_groups, S) scores: one warp per group.
@@ -1070,20 +1078,48 @@ extern "C" int64_t cst_refs_cooked_bytes(int32_t ref_width, int32_t refs_per_vid
     return (raw + 127) / 128 * 128;
 }
 
+template <int MODE, int CTAS, int BASE>
+static cudaError_t score_kernel_smem(size_t smem) {
+    return cudaFuncSetAttribute(k_score<MODE, CTAS, BASE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+}
+template <int MODE, int CTAS>
+static cudaError_t score_kernels_smem(size_t smem) {
+    cudaError_t e = score_kernel_smem<MODE, CTAS, CST_BASE_ANY>(smem);
+    if (CTAS == CST_MIN_CTAS) {
+        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_GREEDY>(smem);
+        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_SCB_GT>(smem);
+        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_SCB_SAMPLE>(smem);
+    }
+    return e;
+}
+
+// MODE raw / staged, full-occupancy build: pick the instantiation specialised for the baseline
+template <int MODE>
+static void launch_throughput(const ScoreParams& p, unsigned grid, int threads, size_t smem, cudaStream_t st) {
+    const bool plain = !p.scores && !p.ref_offsets && ((p.greedy != nullptr) == (p.mode == CST_BASE_GREEDY));
+    if (plain && p.mode == CST_BASE_SCB_SAMPLE)
+        k_score<MODE, CST_MIN_CTAS, CST_BASE_SCB_SAMPLE><<<grid, threads, smem, st>>>(p);
+    else if (plain && p.mode == CST_BASE_SCB_GT)
+        k_score<MODE, CST_MIN_CTAS, CST_BASE_SCB_GT><<<grid, threads, smem, st>>>(p);
+    else if (plain && p.mode == CST_BASE_GREEDY)
+        k_score<MODE, CST_MIN_CTAS, CST_BASE_GREEDY><<<grid, threads, smem, st>>>(p);
+    else
+        k_score<MODE, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
+}
+
 static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st) {
     static thread_local size_t configured[64] = {0};
+    static thread_local int n_sm[64] = {0};
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || configured[dev] < smem) {
-        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, CST_MIN_CTAS>, attr, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, CST_MIN_CTAS>, attr, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_COOK, CST_MIN_CTAS>, attr, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS>, attr, (int)smem));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS>, attr, (int)smem));
+        CUDA_TRY((score_kernels_smem<CST_MODE_RAW, CST_MIN_CTAS>(smem)));
+        CUDA_TRY((score_kernels_smem<CST_MODE_STAGED, CST_MIN_CTAS>(smem)));
+        CUDA_TRY((score_kernels_smem<CST_MODE_RAW, CST_SMALL_BATCH_CTAS>(smem)));
+        CUDA_TRY((score_kernels_smem<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS>(smem)));
+        CUDA_TRY((score_kernel_smem<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY>(smem)));
         if (dev < 64) configured[dev] = smem;
     }
-    static thread_local int n_sm[64] = {0};
     int sms = 148;
     if (dev < 64) {
         if (!n_sm[dev]) CUDA_TRY(cudaDeviceGetAttribute(&n_sm[dev], cudaDevAttrMultiProcessorCount, dev));
@@ -1092,15 +1128,15 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
     const bool small = p.n_videos <= (int64_t)CST_SMALL_BATCH_CTAS * sms;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
     if (p.cook_out)
-        k_score<CST_MODE_COOK, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
     else if (p.cooked && small)
-        k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
     else if (p.cooked)
-        k_score<CST_MODE_STAGED, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
+        launch_throughput<CST_MODE_STAGED>(p, grid, threads, smem, st);
     else if (small)
-        k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS><<<grid, threads, smem, st>>>(p);
+        k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
     else
-        k_score<CST_MODE_RAW, CST_MIN_CTAS><<<grid, threads, smem, st>>>(p);
+        launch_throughput<CST_MODE_RAW>(p, grid, threads, smem, st);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
