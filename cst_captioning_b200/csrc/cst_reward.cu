@@ -565,12 +565,14 @@ struct ScoreParams {
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
 /* shared memory ahead of the per-video table (see k_score): gh_all, red, long_r, tok_all, then the part that
    a staged-reference image mirrors byte for byte: hdr, invn, lenr and, right behind them, the table */
-#define CST_SCORE_WORK_SMEM ((CST_MAX_WARPS * 64 + 2 * CST_MAX_WARPS) * sizeof(double) + 32 * sizeof(int) + \
-                             CST_MAX_WARPS * 32 * sizeof(u32))
+#define CST_WIDE_WARPS 20     /* small batches with more than 20 rows per phase: a CTA of 20 warps, one round */
+#define CST_SCORE_WORK_SMEM_W(W) (((W) * 64 + 2 * (W)) * sizeof(double) + 32 * sizeof(int) + (W) * 32 * sizeof(u32))
+#define CST_SCORE_WORK_SMEM CST_SCORE_WORK_SMEM_W(CST_MAX_WARPS)
 #define CST_IMG_HEAD (4 * sizeof(u32) + 128 * sizeof(double) + 32 * sizeof(int))   /* hdr + invn + lenr */
 #define CST_SCORE_FIXED_SMEM (CST_SCORE_WORK_SMEM + CST_IMG_HEAD)
 #define CST_IMG_MAGIC 0x43535431u   /* "CST1": layout version of a staged-reference image */
-static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_IMG_HEAD % 16 == 0, "the image must stay 16-byte aligned");
+static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) % 16 == 0 && CST_IMG_HEAD % 16 == 0,
+              "the image must stay 16-byte aligned");
 #ifndef CST_MIN_CTAS
 #define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
 #endif
@@ -597,8 +599,8 @@ static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_IMG_HEAD % 16 == 0, "the imag
 // output and uniform ref counts -- the three shapes of a training step), or CST_BASE_ANY: everything
 // decided at run time.  Worth 9 % of the raw-row kernel's instructions and 3 % of its time.
 #define CST_BASE_ANY (-2)
-template <int MODE, int CTAS, int BASE>
-__global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreParams p) {
+template <int MODE, int CTAS, int BASE, int WARPS = CST_MAX_WARPS>
+__global__ void __launch_bounds__(WARPS * 32, CTAS) k_score(const ScoreParams p) {
     const int k_mode = (BASE == CST_BASE_ANY) ? p.mode : BASE;
     const void* const k_greedy = (BASE == CST_BASE_ANY || BASE == CST_BASE_GREEDY) ? p.greedy : nullptr;
     double* const k_scores = (BASE == CST_BASE_ANY) ? p.scores : nullptr;
@@ -618,12 +620,12 @@ __global__ void __launch_bounds__(CST_MAX_WARPS * 32, CTAS) k_score(const ScoreP
     // Fixed-size arrays first, then the table, then the arrays sized by the candidate count: what the
     // item loop touches sits at compile-time offsets (the address arithmetic folds into the
     // instructions instead of being recomputed from tab_slots under register pressure).
-    double* gh_all = reinterpret_cast<double*>(smem);               // [CST_MAX_WARPS][2][32]
-    double* red = gh_all + CST_MAX_WARPS * 64;                      // [2 * CST_MAX_WARPS]
-    int* long_r = reinterpret_cast<int*>(red + 2 * CST_MAX_WARPS);  // [32] long reference rows of the chunk
-    u32* tok_all = reinterpret_cast<u32*>(long_r + 32);             // [CST_MAX_WARPS][32]
+    double* gh_all = reinterpret_cast<double*>(smem);               // [WARPS][2][32]
+    double* red = gh_all + WARPS * 64;                              // [2 * WARPS]
+    int* long_r = reinterpret_cast<int*>(red + 2 * WARPS);          // [32] long reference rows of the chunk
+    u32* tok_all = reinterpret_cast<u32*>(long_r + 32);             // [WARPS][32]
     // hdr .. tab is what phase R produces: contiguous, so a staged-reference image is one copy
-    u32* hdr = tok_all + CST_MAX_WARPS * 32;                        // [4] magic, tab_slots, refs, use_eos
+    u32* hdr = tok_all + WARPS * 32;                                // [4] magic, tab_slots, refs, use_eos
     double* invn = reinterpret_cast<double*>(hdr + 4);              // [4][32]
     int* lenr = reinterpret_cast<int*>(invn + 128);                 // [32]
     VidSlot* tab = reinterpret_cast<VidSlot*>(lenr + 32);           // [tab_slots], 16-byte aligned
@@ -1107,7 +1109,7 @@ static void launch_throughput(const ScoreParams& p, unsigned grid, int threads, 
         k_score<MODE, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
 }
 
-static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st) {
+static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st, int rows_per_phase = 0) {
     static thread_local size_t configured[64] = {0};
     static thread_local int n_sm[64] = {0};
     int dev = 0;
@@ -1118,6 +1120,10 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
         CUDA_TRY((score_kernels_smem<CST_MODE_RAW, CST_SMALL_BATCH_CTAS>(smem)));
         CUDA_TRY((score_kernels_smem<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS>(smem)));
         CUDA_TRY((score_kernel_smem<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY>(smem)));
+        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+        const int wide = (int)(smem + CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) - CST_SCORE_WORK_SMEM);
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, 1, CST_BASE_ANY, CST_WIDE_WARPS>, attr, wide));
+        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, 1, CST_BASE_ANY, CST_WIDE_WARPS>, attr, wide));
         if (dev < 64) configured[dev] = smem;
     }
     int sms = 148;
@@ -1127,6 +1133,20 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
     }
     const bool small = p.n_videos <= (int64_t)CST_SMALL_BATCH_CTAS * sms;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+    // a small batch with more than 20 rows in a phase (BASELINE config 3: 20 sampled + 20 greedy per
+    // video): one CTA of up to 20 warps per video does the phase in one round instead of two
+    const size_t wide_smem = smem + CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) - CST_SCORE_WORK_SMEM;
+    if (small && !p.cook_out && rows_per_phase > 2 * CST_MAX_WARPS && p.n_videos <= sms && wide_smem <= 227 * 1024) {
+        int w = (rows_per_phase + 1) / 2;
+        if (w > CST_WIDE_WARPS) w = CST_WIDE_WARPS;
+        if (p.cooked)
+            k_score<CST_MODE_STAGED, 1, CST_BASE_ANY, CST_WIDE_WARPS><<<grid, w * 32, wide_smem, st>>>(p);
+        else
+            k_score<CST_MODE_RAW, 1, CST_BASE_ANY, CST_WIDE_WARPS><<<grid, w * 32, wide_smem, st>>>(p);
+        COUNT_LAUNCH();
+        CUDA_TRY(cudaGetLastError());
+        return CST_OK;
+    }
     if (p.cook_out)
         k_score<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
     else if (p.cooked && small)
@@ -1241,7 +1261,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
 
     const int threads = nwarps * 32;
-    return launch_score(p, threads, smem, st);
+    return launch_score(p, threads, smem, st, p.chunk_refs > n_local ? p.chunk_refs : n_local);
 }
 
 extern "C" int cst_cider_scores(const cst_df_table* table, const void* cand, const void* greedy,
