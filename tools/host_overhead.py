@@ -20,3 +20,16 @@ for name, fn in (('tensor refs', lambda: cst.get_self_critical_reward(c, gr, r, 
     torch.cuda.synchronize()
     t2 = time.perf_counter()
     print('%s: host %.1f us per call (issue only), %.1f us per call incl. drain' % (name, (t1 - t0) / 2000 * 1e6, (t2 - t0) / 2000 * 1e6))
+
+# where the host time of one call goes
+import cProfile, pstats, io
+fn = lambda: cst.get_self_critical_reward(c, gr, rs, scorer, expand_feat=1, seq_per_img=20, use_eos=1)
+pr = cProfile.Profile()
+pr.enable()
+for _ in range(2000):
+    fn()
+pr.disable()
+torch.cuda.synchronize()
+out = io.StringIO()
+pstats.Stats(pr, stream=out).sort_stats('tottime').print_stats(14)
+print('\n'.join(l[:150] for l in out.getvalue().splitlines()[:30]))
