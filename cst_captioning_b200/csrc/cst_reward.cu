@@ -451,22 +451,13 @@ __device__ __forceinline__ void baseline_group(const double* sc, const double* o
     sum_b = sb;
 }
 
-// Deterministic fold of per-group partials by the last CTA to finish.
-// ctl[0] = CTA arrival counter, ctl[1] = bad-row counter; both return to 0.
-__device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* partials, int64_t n_groups,
-                                                   double n_m, double n_b, double* stats, double* red /*[2*nwarps]*/) {
-    __shared__ int s_last;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const u32 done = atomicAdd(&ctl[0], 1u);
-        s_last = (done == gridDim.x - 1) ? 1 : 0;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
+// The fold itself: thread t adds the groups t, t + blockDim, ...; warps by shuffle tree; the warps'
+// sums in order.  The bits depend on blockDim only, so the in-kernel fold and k_fold_stats agree.
+__device__ __forceinline__ void fold_stats_body(u32* ctl, const double* partials, int64_t n_groups, double n_m,
+                                                double n_b, double* stats, double* red /*[2*nwarps]*/) {
     double am = 0.0, ab = 0.0;
     for (int64_t g = threadIdx.x; g < n_groups; g += blockDim.x) {
+
         am += __ldcg(partials + 2 * g);
         ab += __ldcg(partials + 2 * g + 1);
     }
@@ -488,6 +479,23 @@ __device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* parti
         __threadfence();
         ctl[0] = 0u;
     }
+}
+
+// Deterministic fold of per-group partials by the last CTA to finish.
+// ctl[0] = CTA arrival counter, ctl[1] = bad-row counter; both return to 0.
+__device__ __forceinline__ void fold_stats_if_last(u32* ctl, const double* partials, int64_t n_groups,
+                                                   double n_m, double n_b, double* stats, double* red /*[2*nwarps]*/) {
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const u32 done = atomicAdd(&ctl[0], 1u);
+        s_last = (done == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    fold_stats_body(ctl, partials, n_groups, n_m, n_b, stats, red);
 }
 
 // ---------------------------------------------------------------------------
@@ -520,6 +528,14 @@ __device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, u32 parit
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
     return ok != 0;
+}
+
+// Large batches: the per-CTA arrival protocol (fence, atomic, two barriers) costs every CTA more than one
+// tiny follow-up launch costs the batch, so there the fold is its own kernel (same summation order).
+__global__ void k_fold_stats(u32* ctl, const double* partials, int64_t n_groups, double n_m, double n_b,
+                             double* stats) {
+    extern __shared__ __align__(16) unsigned char fold_smem[];
+    fold_stats_body(ctl, partials, n_groups, n_m, n_b, stats, reinterpret_cast<double*>(fold_smem));
 }
 
 // ---------------------------------------------------------------------------
@@ -560,6 +576,7 @@ struct ScoreParams {
     const int64_t* cooked_index;    // image of video v = cooked_index[v] (NULL: v)
     int64_t cooked_stride;          // bytes per image
     unsigned char* cook_out;        // cooking: no candidates, phase R's result is written out
+    int fold_apart;                 // the statistics are folded by k_fold_stats after this launch
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
@@ -595,6 +612,9 @@ static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_SCORE_WORK_SMEM_W(CST_WIDE_WA
 // the throughput build; 2 (90 registers, no spills) finishes a lone video 15 % sooner and serves
 // batches small enough that two CTAs per SM hold them all (BASELINE configs 1 and 3: 64 videos).
 #define CST_SMALL_BATCH_CTAS 2
+#ifndef CST_FOLD_APART_CTAS
+#define CST_FOLD_APART_CTAS 16   /* batches of at least this many CTAs per SM fold their statistics in k_fold_stats */
+#endif
 // BASE: the baseline a launch is specialised for (CST_BASE_GREEDY / SCB_GT / SCB_SAMPLE, with no scores
 // output and uniform ref counts -- the three shapes of a training step), or CST_BASE_ANY: everything
 // decided at run time.  Worth 9 % of the raw-row kernel's instructions and 3 % of its time.
@@ -1015,7 +1035,7 @@ __global__ void __launch_bounds__(WARPS * 32, CTAS) k_score(const ScoreParams p)
         }
 #endif
     }
-    if (k_mode >= 0) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
+    if (k_mode >= 0 && !p.fold_apart) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
 }
 
 // Standalone baseline over (n_groups, S) scores: one warp per group.
@@ -1109,7 +1129,8 @@ static void launch_throughput(const ScoreParams& p, unsigned grid, int threads, 
         k_score<MODE, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
 }
 
-static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStream_t st, int rows_per_phase = 0) {
+static int launch_score(const ScoreParams& p_in, int threads, size_t smem, cudaStream_t st, int rows_per_phase = 0) {
+    ScoreParams p = p_in;
     static thread_local size_t configured[64] = {0};
     static thread_local int n_sm[64] = {0};
     int dev = 0;
@@ -1147,6 +1168,7 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
         CUDA_TRY(cudaGetLastError());
         return CST_OK;
     }
+    p.fold_apart = (p.mode >= 0 && !p.cook_out && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
     if (p.cook_out)
         k_score<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
     else if (p.cooked && small)
@@ -1159,6 +1181,12 @@ static int launch_score(const ScoreParams& p, int threads, size_t smem, cudaStre
         launch_throughput<CST_MODE_RAW>(p, grid, threads, smem, st);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
+    if (p.fold_apart) {
+        k_fold_stats<<<1, threads, 2 * (threads / 32) * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m,
+                                                                             p.n_b, p.stats);
+        COUNT_LAUNCH();
+        CUDA_TRY(cudaGetLastError());
+    }
     return CST_OK;
 }
 
