@@ -1153,7 +1153,10 @@ static int launch_score(const ScoreParams& p_in, int threads, size_t smem, cudaS
         sms = n_sm[dev];
     }
     const bool small = p.n_videos <= (int64_t)CST_SMALL_BATCH_CTAS * sms;
-    const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+    unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+#ifdef CST_EXPERIMENT
+    if (const char* e = getenv("CST_EXP_GRID")) grid = (unsigned)atoi(e) < grid ? (unsigned)atoi(e) : grid;
+#endif
     // a small batch with more than 20 rows in a phase (BASELINE config 3: 20 sampled + 20 greedy per
     // video): one CTA of up to 20 warps per video does the phase in one round instead of two
     const size_t wide_smem = smem + CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) - CST_SCORE_WORK_SMEM;
