@@ -244,6 +244,8 @@ int cst_reward_noalloc(const cst_df_table* table,
  * 10 k videos: 0.47 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
  * images of the videos named by image_index (device int64, one per video of the batch; NULL =
  * images 0..n_videos-1 in order): a step passes video indices instead of reference rows.
+ * The indices are not range-checked (that would need a host read): every one must name an
+ * image inside the buffer.
  * Images depend on the df table, use_eos, ref_width and refs_per_video they were cooked with;
  * an image of another layout, table geometry or use_eos makes the rewards of that video NaN
  * and is counted in stats_out[4].  At most 32 refs per video (a video with more gets an
