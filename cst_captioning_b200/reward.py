@@ -157,7 +157,10 @@ class CookedRefs:
         if torch.is_tensor(video_ids):
             idx = video_ids.to(self.images.device, torch.int64).contiguous()
         else:
-            idx = torch.from_numpy(np.ascontiguousarray(video_ids, dtype=np.int64)).to(self.images.device)
+            ids = np.ascontiguousarray(video_ids, dtype=np.int64)
+            if ids.size and (ids.min() < 0 or ids.max() >= self.images.shape[0]):
+                raise ValueError('video index outside the %d staged videos' % self.images.shape[0])
+            idx = torch.from_numpy(ids).to(self.images.device)
         return CookedRefs(self.images, self.stride, self.ref_width, self.max_refs, self.use_eos, self.table,
                           index=idx, n_videos=idx.numel(), bad_rows=self.bad_rows)
 
