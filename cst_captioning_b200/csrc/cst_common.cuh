@@ -60,9 +60,11 @@ __host__ __device__ __forceinline__ u32 cst_slot(u32 h, u32 cap) {
 
 #ifdef __CUDACC__
 
-// One bucket = 4 keys = 32 bytes = one sector, fetched by a single LDG.256.
+// One bucket = 4 keys = 32 bytes = one sector, fetched by a single LDG.256.  Not allocated in L1:
+// probes land all over a 36 MB array, and the 28 KB of L1 an SM has left next to four per-video
+// tables are better spent on the token rows and the unigram idf (3.22 -> 3.11 ms).
 __device__ __forceinline__ void ld_bucket(const u64* p, u64 k[4]) {
-    asm volatile("ld.global.nc.v4.u64 {%0,%1,%2,%3}, [%4];"
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3])
                  : "l"(p));
 }
