@@ -36,6 +36,17 @@ def test_header_symbols_are_exported(cst):
     assert cst.lib.cst_abi_version() == 1
 
 
+def test_every_entry_point_is_mapped_to_the_reference_in_the_docs():
+    """INTEGRATION.md names, for each C symbol, the reference interface it replaces; the header
+    cites reference file:line somewhere in the comment above each group of declarations."""
+    doc = open(os.path.join(ROOT, 'INTEGRATION.md')).read()
+    for n in _declared_symbols():
+        assert '`%s`' % n in doc, '%s is missing from INTEGRATION.md' % n
+    header = open(os.path.join(ROOT, 'include', 'cst_reward.h')).read()
+    for cited in ('utils.py:', 'train.py:', 'compute_ciderdf.py:', 'model.py:', 'dataloader.py:'):
+        assert cited in header, 'the header no longer cites %s' % cited
+
+
 def test_scratch_bytes_and_constants(cst):
     assert cst.lib.cst_reward_scratch_bytes(0) == 256
     assert cst.lib.cst_reward_scratch_bytes(65536) == 256 + 16 * 65536
