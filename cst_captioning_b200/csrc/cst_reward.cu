@@ -616,8 +616,8 @@ static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_SCORE_WORK_SMEM_W(CST_WIDE_WA
 #define CST_FOLD_APART_CTAS 16   /* batches of at least this many CTAs per SM fold their statistics in k_fold_stats */
 #endif
 // BASE: the baseline a launch is specialised for (CST_BASE_GREEDY / SCB_GT / SCB_SAMPLE, with no scores
-// output and uniform ref counts -- the three shapes of a training step), or CST_BASE_ANY: everything
-// decided at run time.  Worth 9 % of the raw-row kernel's instructions and 3 % of its time.
+// output, uniform ref counts and int32 rows -- the three shapes of a training step), or CST_BASE_ANY:
+// everything decided at run time.  Worth 10 % of the raw-row kernel's instructions and 5 % of its time.
 #define CST_BASE_ANY (-2)
 template <int MODE, int CTAS, int BASE, int WARPS = CST_MAX_WARPS>
 __global__ void __launch_bounds__(WARPS * 32, CTAS) k_score(const ScoreParams p) {
@@ -759,14 +759,14 @@ __global__ void __launch_bounds__(WARPS * 32, CTAS) k_score(const ScoreParams p)
                         const void* row;
                         int esz, width;
                         if (is_r) {
-                            esz = p.ref_esz;
+                            esz = (BASE == CST_BASE_ANY) ? p.ref_esz : 4;
                             width = p.ref_width;
                             row = reinterpret_cast<const char*>(p.refs) +
                                   (size_t)(c0 + ri) * (size_t)p.ref_stride * (size_t)esz;
                         } else {
                             const bool gq = ri >= p.cands_per_video;
                             const int64_t ci = video * p.cands_per_video + (gq ? ri - p.cands_per_video : ri);
-                            esz = p.cand_esz;
+                            esz = (BASE == CST_BASE_ANY) ? p.cand_esz : 4;
                             width = p.cand_width;
                             row = reinterpret_cast<const char*>(gq ? k_greedy : p.cand) +
                                   (size_t)ci * (size_t)p.cand_stride * (size_t)esz;
@@ -1118,7 +1118,8 @@ static cudaError_t score_kernels_smem(size_t smem) {
 // MODE raw / staged, full-occupancy build: pick the instantiation specialised for the baseline
 template <int MODE>
 static void launch_throughput(const ScoreParams& p, unsigned grid, int threads, size_t smem, cudaStream_t st) {
-    const bool plain = !p.scores && !p.ref_offsets && ((p.greedy != nullptr) == (p.mode == CST_BASE_GREEDY));
+    const bool plain = !p.scores && !p.ref_offsets && ((p.greedy != nullptr) == (p.mode == CST_BASE_GREEDY)) &&
+                       p.cand_esz == 4 && p.ref_esz == 4;
     if (plain && p.mode == CST_BASE_SCB_SAMPLE)
         k_score<MODE, CST_MIN_CTAS, CST_BASE_SCB_SAMPLE><<<grid, threads, smem, st>>>(p);
     else if (plain && p.mode == CST_BASE_SCB_GT)
