@@ -577,6 +577,7 @@ struct ScoreParams {
     int64_t cooked_stride;          // bytes per image
     unsigned char* cook_out;        // cooking: no candidates, phase R's result is written out
     int fold_apart;                 // the statistics are folded by k_fold_stats after this launch
+    u32 list_cap;                   // k_score2: n-gram instances per batch (shared-memory list)
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
@@ -1056,6 +1057,8 @@ __global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, 
     fold_stats_if_last(ctl, partials, n_groups, n_m, n_b, stats, red);
 }
 
+#include "cst_score2.cuh"
+
 // ---------------------------------------------------------------------------
 // host side of scoring
 // ---------------------------------------------------------------------------
@@ -1194,6 +1197,65 @@ static int launch_score(const ScoreParams& p_in, int threads, size_t smem, cudaS
     return CST_OK;
 }
 
+// Which raw-row kernel serves a call: k_score2 (default) or, with CST_KERNEL=1 in the environment, the
+// round-1 kernel k_score (kept: staged references and cooking run on it, and the tests hold the two
+// against each other).
+static int raw_kernel_version() {
+    static const int v = [] {
+        const char* e = getenv("CST_KERNEL");
+        return (e && atoi(e) == 1) ? 1 : 2;
+    }();
+    return v;
+}
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per function and device, shared by all host threads:
+// remember the largest value set so far process-wide and only ever raise it.
+static std::mutex g_smem_mutex;
+static size_t g_smem_set2[64] = {0};
+static int g_sm_count[64] = {0};
+
+static int device_sms(int dev, int* sms) {
+    *sms = 148;
+    if (dev < 0 || dev >= 64) return CST_OK;
+    std::lock_guard<std::mutex> lock(g_smem_mutex);
+    if (!g_sm_count[dev]) CUDA_TRY(cudaDeviceGetAttribute(&g_sm_count[dev], cudaDevAttrMultiProcessorCount, dev));
+    *sms = g_sm_count[dev];
+    return CST_OK;
+}
+
+static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
+    ScoreParams p = p_in;
+    p.tab_slots = CST2_TAB_SLOTS;
+    p.list_cap = CST2_LIST_CAP;
+    const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
+    const size_t smem = score2_smem(n_local, p.cands_per_video, CST2_WARPS);
+    if (smem > 227 * 1024) return fail(CST_E_RANGE, "scoring needs %zu bytes of shared memory per CTA", smem);
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lock(g_smem_mutex);
+        if (dev < 0 || dev >= 64 || g_smem_set2[dev] < smem) {
+            CUDA_TRY(cudaFuncSetAttribute(k_score2<CST2_WARPS, CST2_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
+            if (dev >= 0 && dev < 64) g_smem_set2[dev] = smem;
+        }
+    }
+    int sms = 148;
+    int rc = device_sms(dev, &sms);
+    if (rc != CST_OK) return rc;
+    const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+    p.fold_apart = (p.mode >= 0 && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
+    k_score2<CST2_WARPS, CST2_CTAS><<<grid, CST2_WARPS * 32, smem, st>>>(p);
+    COUNT_LAUNCH();
+    CUDA_TRY(cudaGetLastError());
+    if (p.fold_apart) {
+        k_fold_stats<<<1, 256, 2 * 8 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);
+        COUNT_LAUNCH();
+        CUDA_TRY(cudaGetLastError());
+    }
+    return CST_OK;
+}
+
 static int score_common(const char* who, const cst_df_table* t, const void* cand, const void* greedy,
                         int32_t cand_dtype, int64_t n_cand, int32_t cand_width, int64_t cand_stride,
                         const void* refs, int32_t ref_dtype, int32_t ref_width, int64_t ref_stride,
@@ -1273,6 +1335,7 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
         p.partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
         if (mode >= 0) stat_counts(mode, n_cand, cands_per_video, scb_k, p.n_m, p.n_b);
     }
+    if (!cooked && raw_kernel_version() == 2) return launch_score2(p, st);
     // every n-gram instance of the staged refs gets at most one slot (plus, for an
     // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
     p.tab_slots = table_slots_for(p.chunk_refs, ref_width);
