@@ -578,6 +578,7 @@ struct ScoreParams {
     unsigned char* cook_out;        // cooking: no candidates, phase R's result is written out
     int fold_apart;                 // the statistics are folded by k_fold_stats after this launch
     u32 list_cap;                   // k_score2: n-gram instances per batch (shared-memory list)
+    int prefetch_ahead;             // k_score2: how many videos ahead a CTA prefetches rows into L2
 };
 
 #define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
@@ -1245,6 +1246,7 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     if (rc != CST_OK) return rc;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
     p.fold_apart = (p.mode >= 0 && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
+    p.prefetch_ahead = sms * CST2_CTAS;
     k_score2<CST2_WARPS, CST2_CTAS><<<grid, CST2_WARPS * 32, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
@@ -1335,7 +1337,10 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
         p.partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
         if (mode >= 0) stat_counts(mode, n_cand, cands_per_video, scb_k, p.n_m, p.n_b);
     }
-    if (!cooked && raw_kernel_version() == 2) return launch_score2(p, st);
+    // (k_score2 addresses rows with 32-bit pitches; a caller striding rows 4 GB apart gets k_score)
+    if (!cooked && raw_kernel_version() == 2 && (uint64_t)cand_stride * 8u < (1ull << 32) &&
+        (uint64_t)ref_stride * 8u < (1ull << 32))
+        return launch_score2(p, st);
     // every n-gram instance of the staged refs gets at most one slot (plus, for an
     // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
     p.tab_slots = table_slots_for(p.chunk_refs, ref_width);

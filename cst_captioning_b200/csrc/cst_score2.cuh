@@ -27,15 +27,21 @@
 
 #define CST2_ROWS 32                 /* rows per batch: presence bits of a chunk, lanes of the prefix scan */
 #define CST2_TOK_STRIDE 32
-#define CST2_LIST_CAP 1024           /* n-gram instances per batch (16 B each) */
+#ifndef CST2_LIST_CAP
+#define CST2_LIST_CAP 960            /* n-gram instances per batch (16 B each) */
+#endif
 #ifndef CST2_TAB_SLOTS
-#define CST2_TAB_SLOTS 1472          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
+#define CST2_TAB_SLOTS 1531          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
 #endif
 #ifndef CST2_WARPS
 #define CST2_WARPS 8
 #endif
 #ifndef CST2_CTAS
 #define CST2_CTAS 5
+#endif
+
+#ifndef CST2_PREFETCH
+#define CST2_PREFETCH 1     /* L2 prefetch of the rows a later CTA will start on (measured: 2 % of the step) */
 #endif
 
 typedef unsigned short u16;
@@ -46,19 +52,21 @@ struct __align__(16) RefA {          // what a presence bit needs of its referen
     int pad;
 };
 
-// One warp, one row, lane = raw position (utils.py:135-152).  Writes the canonical token codes
-// (id + 1) to out[0 .. L) and returns L | bad << 8, the same value in every lane.
-__device__ __forceinline__ int v2_canon(int t, bool in, int width, int use_eos, int lane, u16* out) {
-    const bool isbad = in && (t < -1 || t > 65534);
-    const bool term = in && (t == 0 || t == -1 || isbad);      // -1 = padding: ends the row, never emitted
+// One warp, one row, lane = raw position (utils.py:135-152).  `u` = token id + 1 as an unsigned
+// (0: padding id -1 or a lane past the row's width, 1: <end>, 2: <start>, > 65535: id out of range).
+// Writes the canonical token codes to out[0 .. L) and returns L | bad << 8, the same in every lane.
+// Branch-free on purpose: predicates combined with & and |, one pass of three ballots.
+__device__ __forceinline__ int v2_canon(u32 u, int use_eos, int lane, u16* out) {
+    const u32 isbad = u > 65535u;
+    const u32 term = (u - 2u) > 65533u;                        // padding, <end> or a bad id end the row
     const u32 tmask = __ballot_sync(CST_FULL, term);
     const u32 bmask = __ballot_sync(CST_FULL, isbad);
-    const int end = tmask ? (__ffs(tmask) - 1) : width;
-    const bool keep = (lane < end && t != 1) || (use_eos && lane == end && in && t == 0);
+    const int end = __clz(__brev(tmask));                      // first terminator; 32 if there is none
+    const u32 keep = ((u32)(lane < end) & (u32)(u != 2u)) | ((u32)(use_eos != 0) & (u32)(lane == end) & (u32)(u == 1u));
     const u32 kmask = __ballot_sync(CST_FULL, keep);
-    if (keep) out[__popc(kmask & lanemask_lt(lane))] = (u16)((u32)t + 1u);
-    const int bad = (end < 32) ? (int)((bmask >> end) & 1u) : 0;
-    return __popc(kmask) | (bad << 8);
+    if (keep) out[__popc(kmask & lanemask_lt(lane))] = (u16)u;
+    const u32 bad = (u32)(((u64)bmask >> end) & 1ull);
+    return __popc(kmask) | (int)(bad << 8);
 }
 
 // List layout: ORDER-MAJOR.  All unigram instances of the batch come first, then the bigrams, the
@@ -113,7 +121,7 @@ __device__ __forceinline__ int v2_seg(const V2Scan& s, int row, int k) {
 
 // n-gram instances of one row (G = 16: two rows per warp, one per half; G = 32: rows longer than 16).
 // Restates precook (compute_ciderdf.py:28-33) on packed keys: the slot of (order k, position i) holds
-// {key, row | k << 5 | tf << 8} for the first occurrence of an n-gram in the row, zeros for repeats.
+// {key, row | k << 5 | tf << 8} for the first occurrence of an n-gram in the row, meta 0 for repeats.
 template <int G>
 __device__ __forceinline__ void v2_emit(const u16* ctok, int row, int L, const V2Scan& s, uint4* list, int lane) {
     const int sl = lane & (G - 1);
@@ -143,26 +151,16 @@ __device__ __forceinline__ void v2_emit(const u16* ctok, int row, int L, const V
     const u32 hi3 = e2 | (e3 << 16);
     const u32 rowbits = (u32)row;
     uint4* dst = list + sl;
-    const uint4 zero = make_uint4(0, 0, 0, 0);
-    if (sl < L) {
-        const bool lead = (__ffs(ek0) - 1) == sl;
-        dst[ea & 0xffffu] = lead ? make_uint4(e0, 0u, rowbits | ((u32)__popc(ek0) << 8), 0u) : zero;
-    }
-    if (sl + 1 < L) {
-        const bool lead = (__ffs(ek1) - 1) == sl;
-        dst[s.base1 + (ea >> 16)] =
-            lead ? make_uint4(lo1, 0u, rowbits | (1u << 5) | ((u32)__popc(ek1) << 8), 0u) : zero;
-    }
-    if (sl + 2 < L) {
-        const bool lead = (__ffs(ek2) - 1) == sl;
-        dst[s.base2 + (eb & 0xffffu)] =
-            lead ? make_uint4(lo1, e2, rowbits | (2u << 5) | ((u32)__popc(ek2) << 8), 0u) : zero;
-    }
-    if (sl + 3 < L) {
-        const bool lead = (__ffs(ek3) - 1) == sl;
-        dst[s.base3 + (eb >> 16)] =
-            lead ? make_uint4(lo1, hi3, rowbits | (3u << 5) | ((u32)__popc(ek3) << 8), 0u) : zero;
-    }
+    // meta = 0 marks a repeat (tf >= 1 otherwise); the key words are stored either way
+    const u32 sbit = 1u << sl;
+    const u32 m0 = ((ek0 & (0u - ek0)) == sbit) ? (rowbits | ((u32)__popc(ek0) << 8)) : 0u;
+    const u32 m1k = ((ek1 & (0u - ek1)) == sbit) ? (rowbits | (1u << 5) | ((u32)__popc(ek1) << 8)) : 0u;
+    const u32 m2k = ((ek2 & (0u - ek2)) == sbit) ? (rowbits | (2u << 5) | ((u32)__popc(ek2) << 8)) : 0u;
+    const u32 m3k = ((ek3 & (0u - ek3)) == sbit) ? (rowbits | (3u << 5) | ((u32)__popc(ek3) << 8)) : 0u;
+    if (sl < L) dst[ea & 0xffffu] = make_uint4(e0, 0u, m0, 0u);
+    if (sl + 1 < L) dst[s.base1 + (ea >> 16)] = make_uint4(lo1, 0u, m1k, 0u);
+    if (sl + 2 < L) dst[s.base2 + (eb & 0xffffu)] = make_uint4(lo1, e2, m2k, 0u);
+    if (sl + 3 < L) dst[s.base3 + (eb >> 16)] = make_uint4(lo1, hi3, m3k, 0u);
 }
 
 // which of the bucket's four keys equals `key` (-1: none), without branches
@@ -175,12 +173,10 @@ __device__ __forceinline__ int v2_match4(const u64 kk[4], u64 key) {
     return j;
 }
 
-// idf of a packed n-gram of order k >= 1: one 32-byte bucket of the df table.  A probe ends at a
-// bucket with a free slot, or at a full one nothing overflowed from (its first two keys ascend).
-__device__ __forceinline__ double v2_idf_hashed(const DfView& t, u64 key, u32 h) {
-    u64 kk[4];
-    u32 b = cst_slot(h, t.n_buckets);
-    ld_bucket(t.keys + (size_t)b * CST_BUCKET, kk);
+// Slot of `key` in the df table (-1: absent) given its home bucket `b`, already loaded into kk.  A
+// probe ends at a bucket with a free slot, or at a full one nothing overflowed from (its first two
+// keys ascend).
+__device__ __forceinline__ int v2_resolve(const DfView& t, u64 key, u32 b, u64 kk[4]) {
     int j = v2_match4(kk, key);
     bool more = j < 0 && kk[3] != 0ull && !(kk[0] < kk[1]);
 #pragma unroll 1
@@ -190,17 +186,29 @@ __device__ __forceinline__ double v2_idf_hashed(const DfView& t, u64 key, u32 h)
         j = v2_match4(kk, key);
         more = j < 0 && kk[3] != 0ull && !(kk[0] < kk[1]);
     }
-    return (j >= 0) ? __ldg(t.idfv + (size_t)b * CST_BUCKET + j) : t.unseen;
+    return (j >= 0) ? (int)(b * CST_BUCKET) + j : -1;
 }
 
-// the per-video table with a compile-time capacity
+// The per-video table, capacity T (a compile-time constant).  Double hashing: the step of a probe
+// sequence comes from the key's hash as well, so keys that collide in one slot part ways at once and
+// no clusters build up -- what a warp waits for is the LONGEST probe sequence among its 32 lanes, and
+// linear probing's long tail showed there.  T is prime, so every step in [1, T) visits all slots.
+#ifndef CST2_DOUBLE_HASH
+#define CST2_DOUBLE_HASH 1
+#endif
 template <u32 T>
-__device__ __forceinline__ u32 v2_next(u32 idx) {
-    if ((T & (T - 1)) == 0) return (idx + 1) & (T - 1);
-    return (idx + 1 == T) ? 0u : idx + 1;
+__device__ __forceinline__ u32 v2_step(u32 h) {
+    return CST2_DOUBLE_HASH ? 1u + __umulhi(h * 0x9E3779B1u, T - 1u) : 1u;
 }
 template <u32 T>
-__device__ __forceinline__ u32 v2_insert(VidSlot* tab, u32 idx, u64 key) {
+__device__ __forceinline__ u32 v2_next(u32 idx, u32 step) {
+    idx += step;
+    return (idx >= T) ? idx - T : idx;
+}
+template <u32 T>
+__device__ __forceinline__ u32 v2_insert(VidSlot* tab, u32 h, u64 key) {
+    u32 idx = vid_home(h, T);
+    const u32 step = v2_step<T>(h);
 #pragma unroll 1
     for (;;) {
         const u64 cur = *reinterpret_cast<volatile u64*>(&tab[idx].key);
@@ -209,17 +217,19 @@ __device__ __forceinline__ u32 v2_insert(VidSlot* tab, u32 idx, u64 key) {
             const u64 old = atomicCAS(reinterpret_cast<u64*>(&tab[idx].key), 0ull, key);
             if (old == 0ull || old == key) return idx;
         }
-        idx = v2_next<T>(idx);
+        idx = v2_next<T>(idx, step);
     }
 }
 template <u32 T>
-__device__ __forceinline__ int v2_find(const VidSlot* tab, u32 idx, u64 key) {
+__device__ __forceinline__ int v2_find(const VidSlot* tab, u32 h, u64 key) {
+    u32 idx = vid_home(h, T);
+    const u32 step = v2_step<T>(h);
 #pragma unroll 1
     for (;;) {
         const u64 cur = tab[idx].key;
         if (cur == key) return (int)idx;
         if (cur == 0ull) return -1;
-        idx = v2_next<T>(idx);
+        idx = v2_next<T>(idx, step);
     }
 }
 
@@ -227,40 +237,46 @@ __device__ __forceinline__ int v2_find(const VidSlot* tab, u32 idx, u64 key) {
 //   is_r:  publish the instance into the video table (presence bit of its row; exact count under a
 //          synthetic key when the row holds the n-gram more than once), slot <- {(tf idf)^2, 0}
 //   else:  find it, walk the presence bits, slot <- {(tf idf)^2, idf^2 * sum_r min(tf_h, tf_r) tf_r inv_r g_r}
+// (Two slots per thread and round, so that their df-table loads travel together, was measured: slower.)
 template <int NT, u32 T>
 __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint4* list, int n_ent, int base1,
                                            VidSlot* tab, const RefA* refA, const int* sL, const double* s_gauss) {
 #pragma unroll 1
-    for (int i0 = 0; i0 < n_ent; i0 += NT) {
-        const int i = i0 + (int)threadIdx.x;
-        if (i >= n_ent) break;
+    for (int i = (int)threadIdx.x; i < n_ent; i += NT) {
         const uint4 e = list[i];
         const u64 key = (u64)e.x | ((u64)e.y << 32);
         double w2 = 0.0, num = 0.0;
-        if (key != 0ull) {
+        if (e.z != 0u) {                                       // (0: a repeat of an n-gram inside its row)
             const int row = (int)(e.z & 31u);
             const int k = (int)((e.z >> 5) & 3u);
             const int tf = (int)(e.z >> 8);
             const u32 h = cst_hash(key);
             double idf;
-            if (i < base1) idf = __ldg(p.df.uni + (e.x - 1u));      // unigram: token codes are 1 .. 65535
-            else idf = v2_idf_hashed(p.df, key, h);
+            if (i < base1) {                                   // unigram: token codes are 1 .. 65535
+                idf = __ldg(p.df.uni + (e.x - 1u));
+            } else {
+                u64 kk[4];
+                const u32 b = cst_slot(h, p.df.n_buckets);
+                ld_bucket(p.df.keys + (size_t)b * CST_BUCKET, kk);
+                const int slot = v2_resolve(p.df, key, b, kk);
+                idf = (slot >= 0) ? __ldg(p.df.idfv + slot) : p.df.unseen;
+            }
             const double w = (double)tf * idf;                 // counts2vec: vec = tf * idf
             w2 = w * w;                                        // norm += vec ** 2
             // an n-gram every document holds has idf = 0: exact zeros on both sides, no table entry
             if (idf != 0.0) {
                 if (is_r) {
-                    const u32 idx = v2_insert<T>(tab, vid_home(h, T), key);
+                    const u32 idx = v2_insert<T>(tab, h, key);
                     const u32 bit = 1u << row;
                     atomicOr(&tab[idx].P, bit);
                     if (tf > 1) {
                         atomicOr(&tab[idx].M, bit);
                         const u64 ck = count_key(idx, (u32)row);
-                        const u32 j = v2_insert<T>(tab, vid_home(cst_hash(ck), T), ck);
+                        const u32 j = v2_insert<T>(tab, cst_hash(ck), ck);
                         tab[j].P = (u32)tf;
                     }
                 } else {
-                    const int idx = v2_find<T>(tab, vid_home(h, T), key);
+                    const int idx = v2_find<T>(tab, h, key);
                     if (idx >= 0) {
                         const u32 M = tab[idx].M;
                         u32 P = tab[idx].P & ~M;
@@ -280,7 +296,7 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
                             const int r = __ffs(Q) - 1;
                             Q &= Q - 1u;
                             const u64 ck = count_key((u32)idx, (u32)r);
-                            const int j = v2_find<T>(tab, vid_home(cst_hash(ck), T), ck);
+                            const int j = v2_find<T>(tab, cst_hash(ck), ck);
                             const int c = (int)tab[j].P;
                             const int m = (tf < c ? tf : c) * c;             // min(tf_h, tf_r) * tf_r
                             const RefA a = a_k[r];
@@ -297,18 +313,37 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
 }
 
 // shared-memory layout: everything the hot loops touch sits at a compile-time offset
+#define CST2_CTOK_BYTES ((CST2_ROWS * CST2_TOK_STRIDE + 8) * sizeof(u16))
 #define CST2_OFF_LIST ((size_t)CST2_TAB_SLOTS * sizeof(VidSlot))
 #define CST2_OFF_REFA (CST2_OFF_LIST + (size_t)CST2_LIST_CAP * sizeof(uint4))
 #define CST2_OFF_CTOK (CST2_OFF_REFA + 4 * CST2_ROWS * sizeof(RefA))
-#define CST2_OFF_SLR (CST2_OFF_CTOK + (CST2_ROWS * CST2_TOK_STRIDE + 8) * sizeof(u16))
-#define CST2_OFF_SLC (CST2_OFF_SLR + CST2_ROWS * sizeof(int))
-#define CST2_OFF_SC (CST2_OFF_SLC + CST2_ROWS * sizeof(int))
+#define CST2_OFF_SL (CST2_OFF_CTOK + CST2_CTOK_BYTES)
+#define CST2_OFF_SC (CST2_OFF_SL + CST2_ROWS * sizeof(int))
 
+// -DCST2_TIMING: cycles per warp and stage, added up in the scratch buffer (tools/phase_timing2.py;
+// the counters themselves cost time, read the numbers as proportions)
+#ifdef CST2_TIMING
+#define CST2_TICK(id)                        \
+    do {                                     \
+        const long long now_ = clock64();    \
+        acc_[(id)] += now_ - tick_;          \
+        tick_ = now_;                        \
+    } while (0)
+#else
+#define CST2_TICK(id)
+#endif
+
+// Stages of a video: a reference chunk (up to 32 rows / CST2_LIST_CAP instances), then every
+// candidate batch against it, then the next chunk if there is one.  Both kinds of stage run through
+// ONE copy of the code:   load + canonicalise | scan + emit | process   with a CTA barrier after
+// each; a reference stage ends with the norms of its rows, a candidate stage with the sums of its
+// segments.  A video of the training shapes is one stage of each kind.
 template <int NW, int CTAS>
 __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     constexpr int NT = NW * 32;
     constexpr u32 T = CST2_TAB_SLOTS;
     constexpr int PER = (CST2_ROWS + NW - 1) / NW;      // rows a warp canonicalises per batch
+    constexpr int budget = CST2_LIST_CAP;
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double s_gauss[CST_GAUSS_N];
     const int lane = threadIdx.x & 31;
@@ -321,15 +356,15 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     uint4* list = reinterpret_cast<uint4*>(smem + CST2_OFF_LIST);             // [CST2_LIST_CAP]
     RefA* refA = reinterpret_cast<RefA*>(smem + CST2_OFF_REFA);               // [4][32]
     u16* ctok = reinterpret_cast<u16*>(smem + CST2_OFF_CTOK);                 // [32][32] (+ tail pad)
-    int* sLr = reinterpret_cast<int*>(smem + CST2_OFF_SLR);                   // [32] refs: L | bad << 8
-    int* sLc = reinterpret_cast<int*>(smem + CST2_OFF_SLC);                   // [32] candidates
+    int* sL = reinterpret_cast<int*>(smem + CST2_OFF_SL);                     // [32] L | bad << 8 of the batch's rows
     double* sc = reinterpret_cast<double*>(smem + CST2_OFF_SC);               // [n_local]
     double* low = sc + n_local;                                               // [S]
     double* red = low + S;                                                    // [2 * NW]
 
 #pragma unroll 1
     for (int i = threadIdx.x; i < CST_GAUSS_N; i += NT) s_gauss[i] = p.gauss[i];
-    constexpr int budget = CST2_LIST_CAP;
+    const u32 pitch_r = (u32)p.ref_stride * (u32)p.ref_esz;     // (the host checked that both fit 32 bits)
+    const u32 pitch_c = (u32)p.cand_stride * (u32)p.cand_esz;
 
 #pragma unroll 1
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
@@ -342,164 +377,173 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             r1 = r0 + p.refs_per_video;
         }
         const int R = (int)(r1 - r0);
+#if CST2_PREFETCH
+        // CTAs start in blockIdx order, so the video `prefetch_ahead` (= resident CTAs) further on is
+        // the one a CTA will start on about when this one ends: pull its rows into L2 now, and that
+        // CTA's first loads -- a DRAM round trip nothing else in a video can hide -- become L2 hits.
+        if (threadIdx.x == 0 && !p.ref_offsets) {
+            const int64_t v2 = video + p.prefetch_ahead;
+            if (v2 < p.n_videos) {
+                const char* a = reinterpret_cast<const char*>(p.refs) + (size_t)(v2 * p.refs_per_video) * pitch_r;
+                const char* b = reinterpret_cast<const char*>(p.cand) + (size_t)(v2 * S) * pitch_c;
+                const u32 na = ((u32)p.refs_per_video * pitch_r) & ~15u, nb = ((u32)S * pitch_c) & ~15u;
+                if (na && !(reinterpret_cast<uintptr_t>(a) & 15u))
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"(na) : "memory");
+                if (nb && !(reinterpret_cast<uintptr_t>(b) & 15u))
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b), "r"(nb) : "memory");
+            }
+        }
+#endif
+#ifdef CST2_TIMING
+        long long acc_[16];
+        for (int i = 0; i < 16; ++i) acc_[i] = 0;
+        long long tick_ = clock64();
+#endif
 #pragma unroll 1
-        for (int c = threadIdx.x; c < n_local; c += NT) sc[c] = 0.0;
+        for (int c = threadIdx.x; c < n_local; c += NT) sc[c] = 0.0;   // (stage barriers lie before its first use)
         u32 bad_rows = 0;
 
+        int64_t rbase = r0;
+        int cb = -1;                    // < 0: the stage is the reference chunk at rbase; else candidate row cb
+        int nref = 0;
 #pragma unroll 1
-        for (int64_t rbase = r0; rbase < r1;) {
-            // a reference chunk (up to 32 rows / CST2_LIST_CAP instances), then every candidate batch
-            // against it: both kinds of batch run through the same code below (cb < 0: the chunk)
+        while (rbase < r1) {
+            const bool is_r = cb < 0;
+            // ---- load + canonicalise the stage's rows: warp w takes rows w, w + NW, ...; all loads are
+            // issued before any is used ----
+            const int n_try = is_r ? (int)((r1 - rbase) < CST2_ROWS ? (r1 - rbase) : CST2_ROWS)
+                                   : ((n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS);
             {
-                uint4* z = reinterpret_cast<uint4*>(tab);
+                const int esz = is_r ? p.ref_esz : p.cand_esz;
+                const u32 pitch = is_r ? pitch_r : pitch_c;
+                const char* base = is_r ? reinterpret_cast<const char*>(p.refs) + (size_t)rbase * pitch_r
+                                        : reinterpret_cast<const char*>(p.cand) + (size_t)(video * S) * pitch_c;
+                const char* base2 = reinterpret_cast<const char*>(p.greedy) + (size_t)(video * S) * pitch_c;
+                const int first = is_r ? 0 : cb;
+                const int split = is_r ? 0x7fffffff : S;                     // sampled rows first, then greedy
+                const bool in = lane < (is_r ? p.ref_width : p.cand_width);
+                const u32 lane_off = (u32)(lane * esz);
+                u32 u[PER];
+#pragma unroll
+                for (int j = 0; j < PER; ++j) {
+                    const int r = warp + j * NW;
+                    int c = first + r;
+                    const char* src = base;
+                    if (c >= split) { c -= split; src = base2; }
+                    const char* tok = src + ((unsigned long long)(u32)c * (unsigned long long)pitch + lane_off);
+                    u32 v = 0u;
+                    if (r < n_try && in) {
+                        if (esz == 4) {
+                            v = (u32)__ldcs(reinterpret_cast<const int*>(tok)) + 1u;
+                        } else if (esz == 8) {
+                            const long long w = __ldcs(reinterpret_cast<const long long*>(tok));
+                            v = (w < -1 || w > 65534) ? 0xffffffffu : (u32)w + 1u;           // out of range: bad
+                        } else {
+                            v = (u32)(int)__ldcs(reinterpret_cast<const short*>(tok)) + 1u;
+                        }
+                    }
+                    u[j] = v;
+                }
+                if (is_r) {
+                    uint4* z = reinterpret_cast<uint4*>(tab);
 #pragma unroll 2
-                for (u32 i = threadIdx.x; i < T; i += NT) z[i] = make_uint4(0, 0, 0, 0);
+                    for (u32 i = threadIdx.x; i < T; i += NT) z[i] = make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int j = 0; j < PER; ++j) {
+                    const int r = warp + j * NW;
+                    if (r < n_try) {
+                        const int v = v2_canon(u[j], p.use_eos, lane, ctok + r * CST2_TOK_STRIDE);
+                        if (lane == 0) sL[r] = v;
+                    }
+                }
             }
-            V2Scan sr;
-            sr.nfit = 0;
+            CST2_TICK(is_r ? 0 : 6);
+            __syncthreads();
+            CST2_TICK(is_r ? 1 : 7);
+            // ---- scan + emit ----
+            const V2Scan sb = v2_scan(sL, n_try, budget, lane);
+            const int nfit = sb.nfit;
+            // rows with ids outside [-1, 65534]: every reference row once, candidates in the first chunk
+            if (warp == 0 && lane < nfit && (is_r || rbase == r0)) bad_rows += (u32)(sL[lane] >> 8);
 #pragma unroll 1
-            for (int cb = -1; cb < n_local;) {
-                const bool is_r = cb < 0;
-                if (cb == 0 && warp < 4) {
-                    // norms of the chunk's references (their list segments are still in place):
-                    // thread per (row, order), front to back
-                    const int row = threadIdx.x >> 2, k = threadIdx.x & 3;
-                    const int L = __shfl_sync(CST_FULL, sr.L, row);
-                    const int seg0 = v2_seg(sr, row, k);
-                    if (row < sr.nfit) {
-                        const int n = (L > k) ? L - k : 0;
-                        const double2* seg = reinterpret_cast<const double2*>(list + seg0);
-                        double a = 0.0;
+            for (int pair = warp; 2 * pair < nfit; pair += NW) {
+                const int ra = 2 * pair, rb = ra + 1;
+                const int La = __shfl_sync(CST_FULL, sb.L, ra);
+                const int Lb = (rb < nfit) ? __shfl_sync(CST_FULL, sb.L, rb & 31) : 0;
+                if (La <= 16 && Lb <= 16) {
+                    const bool second = (lane >> 4) != 0;
+                    v2_emit<16>(ctok, second ? (rb & 31) : ra, second ? Lb : La, sb, list, lane);
+                } else {
+#pragma unroll 1
+                    for (int q = 0; q < 2; ++q) {
+                        const int Lq = q ? Lb : La;
+                        if (Lq > 0) v2_emit<32>(ctok, ra + q, Lq, sb, list, lane);
+                    }
+                }
+            }
+            CST2_TICK(is_r ? 2 : 8);
+            __syncthreads();
+            CST2_TICK(is_r ? 3 : 9);
+            // ---- process ----
+            v2_process<NT, T>(p, is_r, list, sb.n_ent, sb.base1, tab, refA, sL, s_gauss);
+            CST2_TICK(is_r ? 4 : 10);
+            __syncthreads();
+            CST2_TICK(is_r ? 5 : 11);
+            // ---- thread per (row, order): its list segment, front to back -> reference norms, or the
+            // candidate's norm and numerator.  No barrier follows: the next stage starts by overwriting
+            // ctok / sL, which nothing here reads (the lengths are in sb), and reaches the list only
+            // after its own first barrier.
+            if (warp * 8 < nfit) {
+                const int row = (threadIdx.x >> 2) & 31, k = threadIdx.x & 3;
+                const int L = __shfl_sync(CST_FULL, sb.L, row);
+                const int seg0 = v2_seg(sb, row, k);
+                double a = 0.0, b = 0.0;
+                if (row < nfit) {
+                    const int n = (L > k) ? L - k : 0;
+                    const double2* seg = reinterpret_cast<const double2*>(list + seg0);
 #pragma unroll 2
-                        for (int j = 0; j < n; ++j) a += seg[j].x;
+                    for (int j = 0; j < n; ++j) {
+                        const double2 v = seg[j];
+                        a += v.x;
+                        b += v.y;
+                    }
+                }
+                const double inv = inv_norm_of(a);
+                if (is_r) {
+                    if (row < nfit) {
                         RefA ra;
-                        ra.inv = inv_norm_of(a);
+                        ra.inv = inv;
                         ra.len = (L > 1) ? L - 1 : 0;                        // "length" = bigram count
                         ra.pad = 0;
                         refA[k * CST2_ROWS + row] = ra;
                     }
-                }
-                int n_try, esz, width;
-                int* sL;
-                const char* rows;       // first row of the batch (candidates: the video's first sampled row)
-                size_t pitch;
-                if (is_r) {
-                    n_try = (int)((r1 - rbase) < CST2_ROWS ? (r1 - rbase) : CST2_ROWS);
-                    esz = p.ref_esz;
-                    width = p.ref_width;
-                    sL = sLr;
-                    pitch = (size_t)p.ref_stride * (size_t)esz;
-                    rows = reinterpret_cast<const char*>(p.refs) + (size_t)rbase * pitch;
                 } else {
-                    n_try = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
-                    esz = p.cand_esz;
-                    width = p.cand_width;
-                    sL = sLc;
-                    pitch = (size_t)p.cand_stride * (size_t)esz;
-                    rows = reinterpret_cast<const char*>(p.cand) + (size_t)(video * S) * pitch;
-                }
-                {
-                    // canonicalise: warp w takes rows w, w + NW, ...; their loads are issued together
-                    const bool in = lane < width;
-                    const size_t lane_off = (size_t)(lane * esz);
-                    int t[PER];
-#pragma unroll
-                    for (int j = 0; j < PER; ++j) {
-                        const int r = warp + j * NW;
-                        t[j] = 0;
-                        if (r < n_try) {
-                            const char* row;
-                            if (is_r) {
-                                row = rows + (size_t)r * pitch;
-                            } else {
-                                const int c = cb + r;                        // sampled rows first, then greedy
-                                row = (c >= S) ? reinterpret_cast<const char*>(p.greedy) +
-                                                     (size_t)(video * S + (c - S)) * pitch
-                                               : rows + (size_t)c * pitch;
-                            }
-                            if (in) {
-                                if (esz == 4) {
-                                    t[j] = __ldcs(reinterpret_cast<const int*>(row + lane_off));
-                                } else if (esz == 8) {
-                                    const long long v = __ldcs(reinterpret_cast<const long long*>(row + lane_off));
-                                    t[j] = (v < -1 || v > 65534) ? 0x7fffffff : (int)v;   // out of range: bad
-                                } else {
-                                    t[j] = (int)__ldcs(reinterpret_cast<const short*>(row + lane_off));
-                                }
-                            }
-                        }
-                    }
-#pragma unroll
-                    for (int j = 0; j < PER; ++j) {
-                        const int r = warp + j * NW;
-                        if (r < n_try) {
-                            const int v = v2_canon(t[j], in, width, p.use_eos, lane, ctok + r * CST2_TOK_STRIDE);
-                            if (lane == 0) sL[r] = v;
-                        }
-                    }
-                }
-                __syncthreads();
-                const V2Scan sb = v2_scan(sL, n_try, budget, lane);
-                const int nfit = sb.nfit;
-                // rows with ids outside [-1, 65534]: every reference row once, candidates in the first chunk
-                if (warp == 0 && lane < nfit && (is_r || rbase == r0)) bad_rows += (u32)(sL[lane] >> 8);
-#pragma unroll 1
-                for (int pair = warp; 2 * pair < nfit; pair += NW) {
-                    const int ra = 2 * pair, rb = ra + 1;
-                    const int La = __shfl_sync(CST_FULL, sb.L, ra);
-                    const int Lb = (rb < nfit) ? __shfl_sync(CST_FULL, sb.L, rb & 31) : 0;
-                    if (La <= 16 && Lb <= 16) {
-                        const bool second = (lane >> 4) != 0;
-                        v2_emit<16>(ctok, second ? (rb & 31) : ra, second ? Lb : La, sb, list, lane);
-                    } else {
-#pragma unroll 1
-                        for (int q = 0; q < 2; ++q) {
-                            const int Lq = q ? Lb : La;
-                            if (Lq > 0) v2_emit<32>(ctok, ra + q, Lq, sb, list, lane);
-                        }
-                    }
-                }
-                __syncthreads();
-                v2_process<NT, T>(p, is_r, list, sb.n_ent, sb.base1, tab, refA, sL, s_gauss);
-                __syncthreads();
-                if (is_r) {
-                    sr = sb;
-                    cb = 0;
-                    continue;
-                }
-                if (warp * 8 < nfit) {
-                    // thread per (candidate, order): norm and numerator of its segment, front to back
-                    const int row = (threadIdx.x >> 2) & 31, k = threadIdx.x & 3;
-                    const int L = __shfl_sync(CST_FULL, sb.L, row);
-                    const int seg0 = v2_seg(sb, row, k);
-                    double val = 0.0;
-                    if (row < nfit) {
-                        const int n = (L > k) ? L - k : 0;
-                        const double2* seg = reinterpret_cast<const double2*>(list + seg0);
-                        double a = 0.0, b = 0.0;
-#pragma unroll 2
-                        for (int j = 0; j < n; ++j) {
-                            const double2 v = seg[j];
-                            a += v.x;
-                            b += v.y;
-                        }
-                        val = b * inv_norm_of(a);
-                    }
+                    double val = b * inv;
                     val += __shfl_xor_sync(CST_FULL, val, 1);
                     val += __shfl_xor_sync(CST_FULL, val, 2);
                     if (row < nfit && k == 0) sc[cb + row] += val;
                 }
-                __syncthreads();
-                cb += nfit;
             }
-            rbase += sr.nfit;
+            CST2_TICK(12);
+            if (is_r) {
+                nref = nfit;
+                cb = 0;
+            } else {
+                cb += nfit;
+                if (cb >= n_local) {    // the chunk has met every candidate: next chunk, if any
+                    rbase += nref;
+                    cb = -1;
+                }
+            }
         }
-        if (R == 0 || n_local == 0) __syncthreads();
         if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+        __syncthreads();
 
-        // ---- phase B: scores, baseline (utils.py:292-322), rewards, per-video statistics ----
+        // ---- scores, baseline (utils.py:292-322), rewards, per-video statistics ----
         // np.mean over the 4 orders, / len(refs), * 10 (compute_cider)
         const double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
+        const int k_mode = p.mode;
 #pragma unroll 1
         for (int c = threadIdx.x; c < n_local; c += NT) {
             const double s = (sc[c] * 0.25) * inv_R * 10.0;
@@ -510,7 +554,6 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             }
         }
         __syncthreads();
-        const int k_mode = p.mode;
         if (k_mode >= 0) {
             const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
             const double* x = (k_mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
@@ -565,6 +608,12 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
                 }
             }
         }
+#ifdef CST2_TIMING
+        CST2_TICK(13);
+        if (lane == 0 && p.ctl)
+            for (int i = 0; i < 16; ++i)
+                if (acc_[i]) atomicAdd(reinterpret_cast<unsigned long long*>(p.ctl) + 8 + i, (unsigned long long)acc_[i]);
+#endif
         __syncthreads();
     }
     if (p.mode >= 0 && !p.fold_apart) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
@@ -572,7 +621,7 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
 
 static size_t score2_smem(int n_local, int cands_per_video, int nwarps) {
     return (size_t)CST2_TAB_SLOTS * sizeof(VidSlot) + (size_t)CST2_LIST_CAP * sizeof(uint4) +
-           4 * CST2_ROWS * sizeof(RefA) + (CST2_ROWS * CST2_TOK_STRIDE + 8) * sizeof(u16) +
-           2 * CST2_ROWS * sizeof(int) + (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
+           4 * CST2_ROWS * sizeof(RefA) + CST2_CTOK_BYTES +
+           CST2_ROWS * sizeof(int) + (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
            2 * (size_t)nwarps * sizeof(double);
 }
