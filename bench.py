@@ -130,6 +130,16 @@ def bind_to_gpu_numa_node(index):
     return 0
 
 
+def load_synth():
+    """The synthetic-corpus module WITHOUT importing the package: its __init__ dlopens
+    libcst_reward.so, and the reference arm must not map any of this repo's native code."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('cst_synth', os.path.join(ROOT, 'cst_captioning_b200', 'synth.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def measured_peak():
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     try:
@@ -159,34 +169,45 @@ def _cpu_init(df, n_doc):
 
 
 def _cpu_shard(args):
+    """Oracle port of utils.get_cst_reward on a shard -> (scores, rewards) per caption, float64.
+    The scorer runs once (score_rows is what utils.py:249-284 does); the baseline block of
+    utils.py:292-322 is then applied to those scores through the function's own WXE entry
+    (bcmrscores given, use_mixer=0 -> scores = bcmrscores.copy()), so both come out of one pass."""
     from oracle import reward_oracle
     sampled, refs = args
+    rows = sampled.astype(np.int64)
     gts = [refs[v].astype(np.int64) for v in range(refs.shape[0])]
-    rew, m, b = reward_oracle.get_cst_reward(sampled.astype(np.int64), gts, _CPU['scorer'], expand_feat=1,
-                                             seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1)
-    return float(rew[:, 0].sum())
+    scores = reward_oracle.score_rows(list(rows), gts, _CPU['scorer'], 1, SEQ_PER_IMG, 1)
+    rew, m, b = reward_oracle.get_cst_reward(rows, gts, _CPU['scorer'], bcmrscores=scores.reshape(-1, SEQ_PER_IMG),
+                                             expand_feat=1, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2,
+                                             use_eos=1, use_mixer=0)
+    return np.asarray(scores, dtype=np.float64), rew[:, 0].copy()
 
 
 def cpu_df_dict():
     """df of the bench corpus as the oracle's dict (vectorised: the Python
     compute_doc_freq of the oracle takes ~8 s on this corpus and is not what is timed)."""
-    from cst_captioning_b200 import synth
     from oracle import ciderd_oracle
+    synth = load_synth()
     rng = np.random.default_rng(synth.SEED)
     refs, nw = synth.make_refs(rng, DF_VIDEOS, N_REFS)
     df, n = ciderd_oracle.build_df_from_strings(synth.df_corpus_strings(refs, nw))
     return df, n
 
 
-def run_cpu_sample(batch, n_videos, procs, df_pair):
-    """Oracle port of utils.get_cst_reward on the first n_videos of the batch -> seconds."""
+def run_cpu_sample(batch, n_videos, procs, df_pair, keep=None):
+    """Oracle port of utils.get_cst_reward on the first n_videos of the batch -> seconds.
+    keep (a dict) receives the per-caption scores and rewards of a single-process run."""
     sampled = batch['sampled'][:n_videos * SEQ_PER_IMG]
     refs = batch['refs'][:n_videos]
     if procs <= 1:
         _cpu_init(*df_pair)
         t0 = time.perf_counter()
-        _cpu_shard((sampled, refs))
-        return time.perf_counter() - t0
+        scores, rewards = _cpu_shard((sampled, refs))
+        secs = time.perf_counter() - t0
+        if keep is not None:
+            keep['scores'], keep['rewards'] = scores, rewards
+        return secs
     import multiprocessing as mp
     bounds = np.linspace(0, n_videos, procs + 1).astype(int)
     shards = [(sampled[a * SEQ_PER_IMG:b * SEQ_PER_IMG], refs[a:b]) for a, b in zip(bounds[:-1], bounds[1:]) if b > a]
@@ -201,7 +222,7 @@ def reference_arm(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return 0
-    from cst_captioning_b200 import synth
+    synth = load_synth()
     cores = os.cpu_count() or 1
     df_pair = cpu_df_dict()
     # size one step so that steps + warmup finish in about two minutes
@@ -236,12 +257,26 @@ def reference_arm(args):
 # ---------------------------------------------------------------------------
 # the CUDA arm
 # ---------------------------------------------------------------------------
+def event_ms(fn, steps, barrier):
+    """steps calls of fn bracketed by CUDA events on the current stream -> ms per call."""
+    import torch
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    barrier()
+    return a.elapsed_time(b) / steps
+
+
 def product_arm(args):
     import torch
     import torch.distributed as dist
     import __graft_entry__ as graft
     graft.build()
     import cst_captioning_b200 as cst
+    from cst_captioning_b200 import dist as cdist
     from cst_captioning_b200 import synth
 
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -281,11 +316,18 @@ def product_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
 
-    # ---- device-resident timing --------------------------------------------------
+    # ---- device-resident timing (the headline `value`) -----------------------------
     launches0 = cst.lib.cst_kernel_launches()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -299,30 +341,51 @@ def product_arm(args):
         t_all1.record()
         barrier()
     launches = cst.lib.cst_kernel_launches() - launches0
-    total_ms = t_all0.elapsed_time(t_all1)
+    total_ms = max_over_ranks(t_all0.elapsed_time(t_all1))
     per_step = [a.elapsed_time(b) for a, b in ev]
-    if world > 1:
-        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
     stats = stats.cpu().numpy()
     value = world * n_cap * args.steps / (total_ms * 1e-3)
+    clock_summary = clocks.summary()
 
-    # the dominant (only) kernel of a step is k_score: one launch per step, bracketed by events
-    kern_ms = float(np.mean(per_step)) if world == 1 else float(np.mean(per_step))
+    # the dominant kernel of a step is the scoring kernel: one launch per step (plus the 5 us fold of the
+    # statistics), bracketed by events on the stream it runs on
+    kern_ms = float(np.mean(per_step))
     peak, peak_src = measured_peak()
     achieved = n_cap * BYTES_PER_CAPTION / (kern_ms * 1e-3) / 1e9
-    traffic = ncu_traffic()
+    traffic = ncu_traffic() or {}
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    sm_hz = 1e6 * float(clock_summary.get('sm_mhz') or clock_summary.get('sm_max_mhz') or 1965.0)
+    warp_inst = traffic.get('warp_inst_per_launch')
     roofline = {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                'traffic': traffic['bytes_per_launch'] if traffic else None, 'kernel': 'k_score',
-                'kernel_ms': kern_ms, 'bytes_per_caption': BYTES_PER_CAPTION, 'peak_source': peak_src,
-                'frac_of_nominal_8TBs': achieved / 8000.0}
+                'traffic': traffic.get('bytes_per_launch'), 'traffic_capture': traffic.get('capture'),
+                'kernel': traffic.get('kernel', 'k_score2'), 'kernel_ms': kern_ms,
+                'bytes_per_caption': BYTES_PER_CAPTION, 'peak_source': peak_src,
+                'frac_of_nominal_8TBs': achieved / 8000.0,
+                # what actually binds: warp-instruction issue (the HBM roofline is the one BASELINE.json names)
+                'limiter': 'instruction issue and dependent-load latency, not HBM',
+                'warp_inst_per_caption': (warp_inst / traffic['captions_per_launch']) if warp_inst else None,
+                'issue_frac': (warp_inst / (sms * 4 * sm_hz * kern_ms * 1e-3)) if warp_inst else None,
+                'issue_note': 'executed warp instructions of the ncu capture / (SMs x 4 schedulers x SM clock x '
+                              'live kernel time)'}
 
-    # ---- informational: references staged once (CookedRefs) -------------------------
+    # ---- the reference's own row dtype: int64 (model.py:255-266, create_sequencelabel.py:93) ----
+    d_cand64 = d_cand.long()
+    d_refs64 = cst.RefSet(d_refs.rows.long(), per_video=N_REFS)
+    for _ in range(3):
+        rew64, _, _, _ = cst.get_cst_reward(d_cand64, d_refs64, scorer, **kw)
+    ms64 = event_ms(lambda: cst.get_cst_reward(d_cand64, d_refs64, scorer, **kw), args.steps, barrier)
+    rew64, _, _, _ = cst.get_cst_reward(d_cand64, d_refs64, scorer, **kw)
+    int64_rows = {'value': n_cap / (ms64 * 1e-3), 'unit': UNIT + ' per GPU', 'ms_per_step': ms64,
+                  'bytes_per_caption': 2 * (BYTES_PER_CAPTION - 4) + 4,
+                  'same_bits_as_int32_rows': bool(torch.equal(rew64, rew))}
+    del d_cand64, d_refs64, rew64
+
+    # ---- references staged once (CookedRefs) -----------------------------------------
     # The ground-truth captions of a training set never change, so their half of the kernel can be
     # run once and kept in HBM; a step then passes candidates + video indices.  NOT the headline
     # (that one, like the reference, works the refs up from raw rows every step).
     staged = None
+    e2e_staged = None
     if not args.no_staged:
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         cooked = cst.CookedRefs.cook(d_refs, scorer, use_eos=1)      # first call: module load
@@ -333,14 +396,8 @@ def product_arm(args):
         cooked_b = cooked.batch(torch.arange(n_videos, device=dev))
         for _ in range(3):
             rew_c, _, _, stats_c = cst.get_cst_reward(d_cand, cooked_b, scorer, **kw)
-        barrier()
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s0.record()
-        for _ in range(args.steps):
-            rew_c, _, _, stats_c = cst.get_cst_reward(d_cand, cooked_b, scorer, **kw)
-        s1.record()
-        barrier()
-        ms_c = s0.elapsed_time(s1) / args.steps
+        ms_c = event_ms(lambda: cst.get_cst_reward(d_cand, cooked_b, scorer, **kw), args.steps, barrier)
+        rew_c, _, _, stats_c = cst.get_cst_reward(d_cand, cooked_b, scorer, **kw)
         staged = {'value': n_cap / (ms_c * 1e-3), 'unit': UNIT + ' per GPU', 'ms_per_step': ms_c,
                   'cook_ms_once': c0.elapsed_time(c1), 'image_bytes_per_video': cooked.stride,
                   'images_bytes_total': cooked.nbytes(),
@@ -350,20 +407,27 @@ def product_arm(args):
         pipe_s = cst.HostRewardPipeline(scorer, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=2, use_eos=1,
                                         slices=args.e2e_slices)
         out_s = torch.empty(n_cap, dtype=torch.float32).pin_memory()
-        for i in range(1 + max(3, min(args.steps, 10))):
-            if i == 1:
-                barrier()
-                t0 = time.perf_counter()
+
+        def e2e_staged_step():
             pipe_s(h_cand, cooked_b, out=out_s)
             torch.cuda.synchronize()
-        e2e_staged_s = (time.perf_counter() - t0) / max(3, min(args.steps, 10))
-        staged['e2e'] = {'value': n_cap / e2e_staged_s, 'unit': UNIT + ' per GPU', 'ms_per_step': 1e3 * e2e_staged_s,
-                         'h2d_bytes_per_step': int(h_cand.numel() * 4), 'd2h_bytes_per_step': int(out_s.numel() * 4),
-                         'same_bits_as_raw_rows': bool(torch.equal(out_s.to(dev), rew[:, 0]))}
+
+        e2e_staged_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_staged_step()
+        barrier()
+        e2e_staged_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+        e2e_staged = {'value': world * n_cap / e2e_staged_s, 'unit': UNIT, 'ms_per_step': 1e3 * e2e_staged_s,
+                      'h2d_bytes_per_step': int(h_cand.numel() * 4), 'd2h_bytes_per_step': int(out_s.numel() * 4),
+                      'steps': args.steps,
+                      'same_bits_as_raw_rows': bool(torch.equal(out_s.to(dev), rew[:, 0])),
+                      'note': 'HostRewardPipeline with the references staged on the device once (a training set\'s '
+                              'references are static, dataloader.py:138-139): only candidates go up'}
         del cooked, cooked_b, pipe_s
 
     # ---- end to end through the public API with HOST buffers -----------------------
-    e2e_steps = max(3, min(args.steps, 10))
     out_pin = torch.empty(n_cap, dtype=torch.float32).pin_memory()
     st_pin = torch.empty(7, dtype=torch.float64).pin_memory()       # CST_N_STATS
 
@@ -381,19 +445,16 @@ def product_arm(args):
     e2e_step()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for _ in range(args.steps):
         e2e_step()
     barrier()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e = {'value': world * n_cap * e2e_steps / e2e_s, 'unit': UNIT,
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e = {'value': world * n_cap * args.steps / e2e_s, 'unit': UNIT,
            'h2d_bytes_per_step': int(h_cand.numel() * 4 + h_refs.numel() * 4),
-           'd2h_bytes_per_step': int(out_pin.numel() * 4 + st_pin.numel() * 8), 'steps': e2e_steps,
+           'd2h_bytes_per_step': int(out_pin.numel() * 4 + st_pin.numel() * 8), 'steps': args.steps,
            'api': 'HostRewardPipeline (pinned host rows, %d slices, upload overlapped with scoring)' % args.e2e_slices,
-           'ms_per_step': 1e3 * e2e_s / e2e_steps}
+           'ms_per_step': 1e3 * e2e_s / args.steps,
+           'same_bits_as_device_resident': bool(torch.equal(out_pin.to(dev), rew[:, 0]))}
 
     # informational: the same pipeline fed int16 host rows (ids <= 32767 fit; half the upload)
     h_cand16, h_refs16 = h_cand.to(torch.int16).pin_memory(), h_refs.to(torch.int16).pin_memory()
@@ -406,22 +467,170 @@ def product_arm(args):
     e2e16_step()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for _ in range(args.steps):
         e2e16_step()
     barrier()
     e2e16_s = time.perf_counter() - t0
-    e2e['int16_host_rows'] = {'value': n_cap * e2e_steps / e2e16_s, 'unit': UNIT + ' per GPU', 'ms_per_step': 1e3 * e2e16_s / e2e_steps,
+    e2e['int16_host_rows'] = {'value': n_cap * args.steps / e2e16_s, 'unit': UNIT + ' per GPU',
+                              'ms_per_step': 1e3 * e2e16_s / args.steps,
                               'h2d_bytes_per_step': int(h_cand16.numel() * 2 + h_refs16.numel() * 2)}
+    del h_cand16, h_refs16
+
+    # ---- the fused consumer of the reward (model.py:7-23): streaming kernels, HBM-bound ----
+    criterion = None
+    if world == 1 and not args.no_criterion:
+        # (timed through the C ABI: at 0.08 ms per launch the autograd wrapper's host time would be the number)
+        from cst_captioning_b200 import _lib
+        from cst_captioning_b200.criterion import _scratch_for as crit_scratch
+        t_w = CAND_W
+        seq = d_cand.long()
+        logp = -torch.rand(n_cap, t_w, device=dev)
+        col = rew[:, 0].contiguous()
+        out2 = torch.empty(2, dtype=torch.float32, device=dev)
+        grad = torch.empty(n_cap, t_w, dtype=torch.float32, device=dev)
+        go = torch.ones(1, dtype=torch.float32, device=dev)
+        scr = crit_scratch(dev)
+        stream = torch.cuda.current_stream(dev).cuda_stream
+
+        def crit_fwd():
+            _lib.check(cst.lib.cst_reward_criterion_fwd(
+                seq.data_ptr(), _lib.DTYPE_I64, seq.stride(0), logp.data_ptr(), logp.stride(0), col.data_ptr(), 1, 0,
+                n_cap, t_w, out2.data_ptr(), out2.data_ptr() + 4, scr.data_ptr(), scr.numel(), dev.index, stream))
+
+        def crit_bwd():
+            _lib.check(cst.lib.cst_reward_criterion_bwd(
+                seq.data_ptr(), _lib.DTYPE_I64, seq.stride(0), col.data_ptr(), 1, 0, out2.data_ptr() + 4,
+                go.data_ptr(), n_cap, t_w, grad.data_ptr(), grad.stride(0), dev.index, stream))
+
+        for _ in range(3):
+            crit_fwd()
+            crit_bwd()
+        f_ms = event_ms(crit_fwd, args.steps, barrier)
+        b_ms = event_ms(crit_bwd, args.steps, barrier)
+        # ... and the module gives the same loss (the path a training loop takes)
+        loss = cst.RewardCriterion()(seq, logp, rew)
+        nbytes = n_cap * t_w * (8 + 4) + n_cap * 4       # int64 seq + fp32 logp (bwd: fp32 grad) + reward column
+        criterion = {'rows': n_cap, 'width': t_w, 'fwd_ms': f_ms, 'bwd_ms': b_ms,
+                     'fwd_GBs': nbytes / f_ms / 1e6, 'bwd_GBs': nbytes / b_ms / 1e6,
+                     'fwd_frac': nbytes / f_ms / 1e6 / peak, 'bwd_frac': nbytes / b_ms / 1e6 / peak,
+                     'bound': 'hbm', 'bytes_per_token': 12,
+                     'module_loss_equals_abi_loss': bool(float(loss) == float(out2[0]))}
+        del seq, logp, loss, grad
+
+    # ---- multi-GPU legs BASELINE.json lists beside the weak sweep (N > 1 only) --------------
+    strong = None
+    config4 = None
+    if world > 1:
+        # strong scaling + hardware parity: ONE global batch (seed 1000, args.videos videos) cut by
+        # dist.shard_range; rank 0 also scores all of it alone, and every rank holds its slice of the
+        # rewards and the all-reduced means against that single-GPU result
+        g = synth.make_batch(args.videos, SEQ_PER_IMG, N_REFS, seed=1000)
+        lo, hi = cdist.shard_range(args.videos, rank, world)
+        s_cand = torch.from_numpy(g['sampled'][lo * SEQ_PER_IMG:hi * SEQ_PER_IMG]).to(dev)
+        s_refs = cst.RefSet(torch.from_numpy(g['refs'][lo:hi]).to(dev).reshape((hi - lo) * N_REFS, REF_W),
+                            per_video=N_REFS)
+
+        def strong_step():
+            r_, _, _, st_ = cst.get_cst_reward(s_cand, s_refs, scorer, **kw)
+            dist.all_reduce(st_)
+            return r_, st_
+
+        for _ in range(3):
+            strong_step()
+        ms_s = max_over_ranks(event_ms(strong_step, args.steps, barrier))
+        r_s, st_s = strong_step()
+        full = torch.empty(args.videos * SEQ_PER_IMG, dtype=torch.float32, device=dev)
+        ref_stats = torch.empty(7, dtype=torch.float64, device=dev)
+        if rank == 0:
+            f_cand = torch.from_numpy(g['sampled']).to(dev)
+            f_refs = cst.RefSet(torch.from_numpy(g['refs']).to(dev).reshape(args.videos * N_REFS, REF_W),
+                                per_video=N_REFS)
+            r_f, _, _, st_f = cst.get_cst_reward(f_cand, f_refs, scorer, **kw)
+            full.copy_(r_f[:, 0])
+            ref_stats.copy_(st_f)
+            del f_cand, f_refs
+        dist.broadcast(full, 0)
+        dist.broadcast(ref_stats, 0)
+        bad = torch.tensor([0 if torch.equal(r_s[:, 0], full[lo * SEQ_PER_IMG:hi * SEQ_PER_IMG]) else 1],
+                           device=dev, dtype=torch.float64)
+        dist.all_reduce(bad)
+        m_n, b_n = float(st_s[0] / st_s[2]), float(st_s[1] / st_s[3])
+        m_1, b_1 = float(ref_stats[0] / ref_stats[2]), float(ref_stats[1] / ref_stats[3])
+        strong = {'value': args.videos * SEQ_PER_IMG / (ms_s * 1e-3), 'unit': UNIT, 'ms_per_step': ms_s,
+                  'global_videos': args.videos, 'videos_per_gpu': hi - lo, 'scaling': 'strong',
+                  'm_score': m_n, 'b_score': b_n, 'm_score_1gpu': m_1, 'b_score_1gpu': b_1,
+                  'm_rel_diff': abs(m_n - m_1) / abs(m_1), 'b_rel_diff': abs(b_n - b_1) / abs(b_1),
+                  'ranks_whose_rewards_differ_from_1gpu': int(bad.item()),
+                  'ok': bool(bad.item() == 0 and abs(m_n - m_1) <= 1e-12 * abs(m_1) and abs(b_n - b_1) <= 1e-12 * abs(b_1))}
+        del s_cand, s_refs, full
+
+        # BASELINE configs[3]: SCB with the baseline from precomputed GT consensus scores, batch 512
+        # sharded over the ranks (64 videos per GPU at 8): per-step latency, where launch + all-reduce
+        # are what is left
+        g4 = synth.make_batch(512, SEQ_PER_IMG, N_REFS, seed=13)
+        lo4, hi4 = cdist.shard_range(512, rank, world)
+        c4 = torch.from_numpy(g4['sampled'][lo4 * SEQ_PER_IMG:hi4 * SEQ_PER_IMG]).to(dev)
+        r4 = torch.from_numpy(g4['refs'][lo4:hi4]).to(dev)
+        bc4 = torch.from_numpy(np.random.default_rng(4).random((512, SEQ_PER_IMG))[lo4:hi4]).to(dev)
+        kw4 = dict(bcmrscores=bc4, expand_feat=1, seq_per_img=SEQ_PER_IMG, scb_captions=20, scb_baseline=1, use_eos=1,
+                   use_mixer=1, return_stats=True)
+
+        def c4_step(reduce=True):
+            r_, _, _, st_ = cst.get_cst_reward(c4, r4, scorer, **kw4)
+            if reduce:
+                dist.all_reduce(st_)
+            return st_
+
+        for _ in range(10):
+            c4_step()
+        ms_red = max_over_ranks(event_ms(c4_step, 200, barrier))
+        ms_lazy = max_over_ranks(event_ms(lambda: c4_step(False), 200, barrier))
+        side = torch.cuda.Stream(dev)
+        with torch.cuda.stream(side):
+            c4_step(False)
+        side.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            keep4 = c4_step(False)
+        ms_graph = max_over_ranks(event_ms(graph.replay, 200, barrier))
+        config4 = {'workload': 'BASELINE.json configs[3]: SCB (GT-consensus baseline), batch 512 sharded over the ranks',
+                   'videos_per_gpu': hi4 - lo4, 'captions_per_step': 512 * SEQ_PER_IMG,
+                   'ms_per_step_with_allreduce': ms_red, 'ms_per_step_stats_reduced_lazily': ms_lazy,
+                   'ms_per_step_cuda_graph_replay_no_collective': ms_graph,
+                   'captions_per_s_with_allreduce': 512 * SEQ_PER_IMG / (ms_red * 1e-3),
+                   'note': 'the statistics are only read every print_log_interval steps (train.py:229-233), so the '
+                           'all-reduce can wait until then: the lazy figures are a step without it'}
+        del graph, keep4
 
     # ---- CPU baseline: oracle port, one core, bounded sample (rank 0, N = 1 only) --
+    # ... and a parity check of the GPU step at the bench's own size against that sample
     cpu = None
+    check = {'m_score': float(stats[0] / stats[2]), 'b_score': float(stats[1] / stats[3]),
+             'bad_rows': float(stats[4]), 'df_ngrams': len(table)}
+    ok = True
     if rank == 0 and world == 1 and not args.no_cpu:
-        n_s = args.cpu_videos
-        secs = run_cpu_sample(batch, n_s, 1, cpu_df_dict())
+        n_s = min(args.cpu_videos, n_videos)
+        keep = {}
+        secs = run_cpu_sample(batch, n_s, 1, cpu_df_dict(), keep)
         cpu = {'value': n_s * SEQ_PER_IMG / secs, 'unit': UNIT, 'cores': 1, 'kind': 'port',
                'sample': 'first %d videos (%d captions) of the step batch, oracle port of utils.get_cst_reward '
                          '+ restated CiderD, %.1f s' % (n_s, n_s * SEQ_PER_IMG, secs),
                'host_cores_available': os.cpu_count()}
+        # float64 scores of the same videos from the CUDA path (cst_cider_scores), and the float32 rewards of
+        # the timed step itself
+        sub = cst.RefSet(d_refs.rows[:n_s * N_REFS], per_video=N_REFS)
+        g_scores = scorer.score_rows(d_cand[:n_s * SEQ_PER_IMG], sub, SEQ_PER_IMG, use_eos=1).cpu().numpy()
+        g_rew = rew[:n_s * SEQ_PER_IMG, 0].double().cpu().numpy()
+        c_scores, c_rew = keep['scores'], keep['rewards']
+        nz = np.abs(c_scores) > 0
+        rel = np.zeros_like(c_scores)
+        rel[nz] = np.abs(g_scores[nz] - c_scores[nz]) / np.abs(c_scores[nz])
+        zeros_agree = bool(np.all(g_scores[~nz] == 0.0))
+        rew_err = float(np.max(np.abs(g_rew - c_rew.astype(np.float32).astype(np.float64))))
+        ok = bool(rel.max() <= 1e-5 and zeros_agree and rew_err <= 1e-5)
+        check.update({'n_compared': int(c_scores.size), 'max_rel_err': float(rel.max()), 'tolerance': 1e-5,
+                      'zero_scores_agree': zeros_agree, 'max_abs_err_reward_f32': rew_err, 'ok': ok,
+                      'against': 'float64 scores of the oracle port on the first %d videos of this very batch' % n_s})
 
     if rank == 0:
         line = {
@@ -429,13 +638,16 @@ def product_arm(args):
             'warmup': max(args.warmup, 3), 'ms_per_step': total_ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
             'config': workload_config(n_videos, world), 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e,
-            'gpu_launches': int(launches), 'clocks': clocks.summary(), 'staged_refs': staged,
-            'check': {'m_score': float(stats[0] / stats[2]), 'b_score': float(stats[1] / stats[3]),
-                      'bad_rows': float(stats[4]), 'df_ngrams': len(table)},
+            'gpu_launches': int(launches), 'clocks': clock_summary, 'int64_rows': int64_rows,
+            'staged_refs': staged, 'e2e_staged': e2e_staged, 'criterion': criterion, 'strong': strong,
+            'config4': config4, 'check': check,
         }
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+    if not ok:
+        sys.stderr.write('bench.py: the GPU step does not match the CPU port on the sampled videos\n')
+        return 1
     return 0
 
 
@@ -449,6 +661,7 @@ def main():
     ap.add_argument('--cpu-videos', type=int, default=640, help='CPU-baseline sample size (videos)')
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-staged', action='store_true', help='skip the informational staged-references leg')
+    ap.add_argument('--no-criterion', action='store_true', help='skip the RewardCriterion leg')
     ap.add_argument('--e2e-slices', type=int, default=16, help='video slices of the host pipeline')
     args = ap.parse_args()
     if args.impl == 'reference':
