@@ -163,6 +163,17 @@ class DfTable:
         check(lib.cst_df_export(self.handle, keys.ctypes.data, df.ctypes.data))
         return keys, df
 
+    def max_token_id(self):
+        """Largest token id any stored n-gram holds (-1 for an empty table); computed once."""
+        if getattr(self, '_max_token', None) is None:
+            keys, _ = self.export()
+            m = 0
+            for shift in (0, 16, 32, 48):
+                if len(keys):
+                    m = max(m, int(((keys >> np.uint64(shift)) & np.uint64(0xffff)).max()))
+            self._max_token = m - 1
+        return self._max_token
+
     def to_pickle(self, path):
         """Write the table in the reference's schema (``compute_ciderdf.py:123-129``)
         so the reference's own scorer can consume a device-built table."""
