@@ -581,464 +581,11 @@ struct ScoreParams {
     int prefetch_ahead;             // k_score2: how many videos ahead a CTA prefetches rows into L2
 };
 
-#define CST_MAX_WARPS 10      /* 10 warps x 2 rows = the 20 refs / 20 candidates of a video */
-/* shared memory ahead of the per-video table (see k_score): gh_all, red, long_r, tok_all, then the part that
-   a staged-reference image mirrors byte for byte: hdr, invn, lenr and, right behind them, the table */
-#define CST_WIDE_WARPS 20     /* small batches with more than 20 rows per phase: a CTA of 20 warps, one round */
-#define CST_SCORE_WORK_SMEM_W(W) (((W) * 64 + 2 * (W)) * sizeof(double) + 32 * sizeof(int) + (W) * 32 * sizeof(u32))
-#define CST_SCORE_WORK_SMEM CST_SCORE_WORK_SMEM_W(CST_MAX_WARPS)
-#define CST_IMG_HEAD (4 * sizeof(u32) + 128 * sizeof(double) + 32 * sizeof(int))   /* hdr + invn + lenr */
-#define CST_SCORE_FIXED_SMEM (CST_SCORE_WORK_SMEM + CST_IMG_HEAD)
-#define CST_IMG_MAGIC 0x43535431u   /* "CST1": layout version of a staged-reference image */
-static_assert(CST_SCORE_WORK_SMEM % 16 == 0 && CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) % 16 == 0 && CST_IMG_HEAD % 16 == 0,
-              "the image must stay 16-byte aligned");
-#ifndef CST_MIN_CTAS
-#define CST_MIN_CTAS 4        /* resident CTAs per SM the register allocation is held to */
-#endif
-
-// One CTA per video.  The body of the item loop exists ONCE in the code and serves
-//   phase 0 (R): the video's reference rows  -> per-video shared table, norms, lengths
-//   phase 1 (C): its candidate rows          -> scores
-// each in two passes: pass 0 handles two rows per warp (lane groups of 16), pass 1 the
-// rows longer than 16 tokens that pass 0 left aside, one row per warp -- or, when only
-// a few rows are long, one n-gram ORDER of a row per warp, so the extra pass is short
-// for the whole CTA.  Keeping a single copy matters: the kernel was instruction-fetch
-// bound when the four combinations were separate instantiations.
-// MODE: which phases a launch runs.  The raw-row kernel (both phases) is sensitive to its instruction
-// footprint, so the two staged-reference variants are separate instantiations that drop the
-// other phase's code instead of branches inside it.
-#define CST_MODE_RAW 0      /* phase R from the reference rows, phase C, phase B */
-#define CST_MODE_STAGED 1   /* phase R replaced by the copy of the video's image (cst_refs_cook) */
-#define CST_MODE_COOK 2     /* phase R only; its result is written out as the video's image */
-// CTAS: resident CTAs per SM the register allocation is held to.  CST_MIN_CTAS (4: 48 registers) is
-// the throughput build; 2 (90 registers, no spills) finishes a lone video 15 % sooner and serves
-// batches small enough that two CTAs per SM hold them all (BASELINE configs 1 and 3: 64 videos).
-#define CST_SMALL_BATCH_CTAS 2
 #ifndef CST_FOLD_APART_CTAS
 #define CST_FOLD_APART_CTAS 16   /* batches of at least this many CTAs per SM fold their statistics in k_fold_stats */
 #endif
-// BASE: the baseline a launch is specialised for (CST_BASE_GREEDY / SCB_GT / SCB_SAMPLE, with no scores
-// output, uniform ref counts and int32 rows -- the three shapes of a training step), or CST_BASE_ANY:
-// everything decided at run time.  Worth 10 % of the raw-row kernel's instructions and 5 % of its time.
-#define CST_BASE_ANY (-2)
-template <int MODE, int CTAS, int BASE, int WARPS = CST_MAX_WARPS>
-__global__ void __launch_bounds__(WARPS * 32, CTAS) k_score(const ScoreParams p) {
-    const int k_mode = (BASE == CST_BASE_ANY) ? p.mode : BASE;
-    const void* const k_greedy = (BASE == CST_BASE_ANY || BASE == CST_BASE_GREEDY) ? p.greedy : nullptr;
-    double* const k_scores = (BASE == CST_BASE_ANY) ? p.scores : nullptr;
-    const int64_t* const k_offsets = (BASE == CST_BASE_ANY) ? p.ref_offsets : nullptr;
-    extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int s_nlong[2];                       // rows too long for a 16-lane group: refs of the chunk / candidates
-    __shared__ int s_ticket[2];                      // next item of the phase's work list
-    __shared__ int s_started[2];                     // pair items past their canonicalisation
-    __shared__ int s_done_r;                         // reference items fully published
-    __shared__ unsigned long long s_img_bar;         // staged references: completion of the image fetch
-    __shared__ double s_gauss[CST_GAUSS_N];          // length-penalty LUT (a global load here would be an L2 trip)
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const int nwarps = blockDim.x >> 5;
-    const int n_local = p.cands_per_video * ((BASE == CST_BASE_GREEDY || k_greedy) ? 2 : 1);
 
-    // Fixed-size arrays first, then the table, then the arrays sized by the candidate count: what the
-    // item loop touches sits at compile-time offsets (the address arithmetic folds into the
-    // instructions instead of being recomputed from tab_slots under register pressure).
-    double* gh_all = reinterpret_cast<double*>(smem);               // [WARPS][2][32]
-    double* red = gh_all + WARPS * 64;                              // [2 * WARPS]
-    int* long_r = reinterpret_cast<int*>(red + 2 * WARPS);          // [32] long reference rows of the chunk
-    u32* tok_all = reinterpret_cast<u32*>(long_r + 32);             // [WARPS][32]
-    // hdr .. tab is what phase R produces: contiguous, so a staged-reference image is one copy
-    u32* hdr = tok_all + WARPS * 32;                                // [4] magic, tab_slots, refs, use_eos
-    double* invn = reinterpret_cast<double*>(hdr + 4);              // [4][32]
-    int* lenr = reinterpret_cast<int*>(invn + 128);                 // [32]
-    VidSlot* tab = reinterpret_cast<VidSlot*>(lenr + 32);           // [tab_slots], 16-byte aligned
-    double* sc = reinterpret_cast<double*>(tab + p.tab_slots);      // [n_local]
-    double* low = sc + n_local;                                     // [cands_per_video]
-    double* part = low + p.cands_per_video;                         // [n_local][4] long-row partial scores
-    int* long_c = reinterpret_cast<int*>(part + 4 * n_local);       // [n_local] long candidate rows
-    double* gh = gh_all + warp * 64;
-    u32* tokbuf = tok_all + warp * 32;
-
-    for (int i = threadIdx.x; i < CST_GAUSS_N; i += blockDim.x) s_gauss[i] = p.gauss[i];
-    // (visible to the CTA after the __syncthreads that follows the first table clear)
-    u32 img_parity = 0;
-    if (MODE == CST_MODE_STAGED) {
-        if (threadIdx.x == 0) mbar_init(&s_img_bar, 1);
-        __syncthreads();
-    }
-
-    for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
-#ifdef CST_PHASE_TIMING
-        long long tk[6];
-        tk[0] = clock64();
-#define CST_TICK(i) tk[i] = clock64()
-#else
-#define CST_TICK(i)
-#endif
-        int64_t r0, r1;
-        if (k_offsets) {
-            r0 = k_offsets[video];
-            r1 = k_offsets[video + 1];
-        } else {
-            r0 = video * p.refs_per_video;
-            r1 = r0 + p.refs_per_video;
-        }
-        int R = (int)(r1 - r0);
-        for (int c = threadIdx.x; c < n_local; c += blockDim.x) sc[c] = 0.0;
-        u32 bad_rows = 0;
-        bool bad_image = false;
-
-        for (int64_t c0 = r0; c0 < r1; c0 += p.chunk_refs) {
-            int nref = (int)((r1 - c0) < (int64_t)p.chunk_refs ? (r1 - c0) : (int64_t)p.chunk_refs);
-            {   // clear the video table (or fetch the staged one) and reset the work-list counters
-                if (MODE == CST_MODE_STAGED) {
-                    // one bulk copy by the copy engine: header, ref norms, ref lengths and table land
-                    // while the warps canonicalise and look up their candidates (the wait is where
-                    // phase C otherwise waits for the reference items)
-                    if (threadIdx.x == 0) {
-                        const int64_t img = p.cooked_index ? p.cooked_index[video] : video;
-                        bulk_fetch(hdr, p.cooked + (size_t)img * (size_t)p.cooked_stride,
-                                   (u32)CST_IMG_HEAD + p.tab_slots * (u32)sizeof(VidSlot), &s_img_bar);
-                    }
-                } else {
-                    uint4* z = reinterpret_cast<uint4*>(tab);
-                    for (u32 i = threadIdx.x; i < p.tab_slots; i += blockDim.x) z[i] = make_uint4(0, 0, 0, 0);
-                }
-                if (threadIdx.x < 2) {
-                    s_nlong[threadIdx.x] = 0;
-                    s_ticket[threadIdx.x] = 0;
-                    s_started[threadIdx.x] = 0;
-                }
-                if (threadIdx.x == 2) s_done_r = 0;
-            }
-            __syncthreads();
-            CST_TICK(1);
-            bool refs_ready = false;                     // warp-uniform
-
-#pragma unroll 1
-            for (int phase = (MODE == CST_MODE_STAGED) ? 1 : 0; phase < ((MODE == CST_MODE_COOK) ? 1 : 2); ++phase) {
-                const bool is_r = (MODE == CST_MODE_COOK) || (MODE == CST_MODE_RAW && phase == 0);
-                // One dynamic work list per phase: first the row pairs (two rows per warp, lane groups
-                // of 16), then the rows the pairs found too long for 16 lanes -- a long row is one item
-                // or, when few rows are long, four items (one n-gram order each).  Warps draw tickets,
-                // so whoever finishes a pair early takes a long-row item instead of idling at a barrier.
-                // The list of long rows is complete once every pair item is past its canonicalisation
-                // (s_started == n_pairs); a warp that wants a long-row item waits for that, which is
-                // brief and cannot deadlock: pair tickets are all drawn before any long-row ticket, and
-                // a pair item reaches that point without waiting on anybody.
-                const int n_items = is_r ? nref : n_local;
-                int* long_list = is_r ? long_r : long_c;
-                const int n_pairs = (n_items + 1) >> 1;
-                int nl = 0;
-                bool split = false;
-#pragma unroll 1
-                for (;;) {
-                    int q = 0;
-                    if (lane == 0) q = atomicAdd(&s_ticket[phase], 1);
-                    q = __shfl_sync(CST_FULL, q, 0);
-                    // ---- which row does this lane group work on? ----
-                    int G, ri, only = -1, slot = 0;
-                    bool act = true;
-                    if (q < n_pairs) {
-                        G = 16;
-                        ri = 2 * q + (lane >> 4);
-                        act = ri < n_items;
-                        if (!act) ri = 2 * q;
-                    } else {
-                        if (lane == 0) {
-                            while (*reinterpret_cast<volatile int*>(&s_started[phase]) < n_pairs) __nanosleep(32);
-                        }
-                        __syncwarp();
-                        nl = *reinterpret_cast<volatile int*>(&s_nlong[phase]);
-                        split = nl * 2 <= nwarps;
-                        if (q >= n_pairs + (split ? nl * 4 : nl)) break;
-                        G = 32;
-                        const int j = q - n_pairs;
-                        slot = split ? (j >> 2) : j;
-                        only = split ? (j & 3) : -1;
-                        ri = *reinterpret_cast<volatile int*>(&long_list[slot]);
-                    }
-                    {
-                        const void* row;
-                        int esz, width;
-                        if (is_r) {
-                            esz = (BASE == CST_BASE_ANY) ? p.ref_esz : 4;
-                            width = p.ref_width;
-                            row = reinterpret_cast<const char*>(p.refs) +
-                                  (size_t)(c0 + ri) * (size_t)p.ref_stride * (size_t)esz;
-                        } else {
-                            const bool gq = ri >= p.cands_per_video;
-                            const int64_t ci = video * p.cands_per_video + (gq ? ri - p.cands_per_video : ri);
-                            esz = (BASE == CST_BASE_ANY) ? p.cand_esz : 4;
-                            width = p.cand_width;
-                            row = reinterpret_cast<const char*>(gq ? k_greedy : p.cand) +
-                                  (size_t)ci * (size_t)p.cand_stride * (size_t)esz;
-                        }
-                        if (!act) width = 0;                         // idle half of an odd pair
-
-                        // ---- front, common to references and candidates ----
-                        u64 key[4];
-                        int L;
-                        const bool bad = canon_row(row, esz, width, p.use_eos, lane, G, tokbuf, key, L);
-                        const int sl = grp_sl(lane, G);
-                        const bool live = act && L <= G;             // G = 16: longer rows become items of their own
-                        if (G == 16) {
-                            if (act && !live && sl == 0) long_list[atomicAdd(&s_nlong[phase], 1)] = ri;
-                            __syncwarp();
-                            if (lane == 0) {
-                                __threadfence_block();               // the list entries before the count
-                                atomicAdd(&s_started[phase], 1);
-                            }
-                        }
-                        int tf[4];
-                        bool lead[4];
-                        row_tf(key, lane, G, only, tf, lead);
-                        u32 h[4];
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) h[k] = cst_hash(key[k]);
-                        double idf[4];
-                        df_probe4<MODE != CST_MODE_RAW>(p.df, key, h, lead, idf);
-                        double n2[4];
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const double w = lead[k] ? (double)tf[k] * idf[k] : 0.0;   // counts2vec: vec = tf * idf
-                            n2[k] = w * w;                                             // norm += vec ** 2
-                            // an n-gram every document holds (<end>, the commonest words) has idf = 0:
-                            // its tf-idf entries are exact zeros on both sides, so it needs no table entry
-                            // and no probe -- and it is the one n-gram that sits in ALL refs of a video
-                            lead[k] = lead[k] && idf[k] != 0.0;
-                        }
-                        const double inv = inv_norm_of(group_sum4_transposed(n2, lane, G));   // own order's 1/norm
-                        const int o = group_order(lane, G);
-
-                        if (is_r) {
-                            // ---- phase R: publish the row into the video table ----
-                            const u32 bit = 1u << ri;
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                if (lead[k]) {
-                                    const u32 idx = vid_insert(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
-                                    atomicOr(&tab[idx].P, bit);
-                                    if (tf[k] > 1) {
-                                        atomicOr(&tab[idx].M, bit);
-                                        const u64 ck = count_key(idx, (u32)ri);
-                                        const u32 j = vid_insert(tab, p.tab_slots,
-                                                                 vid_home(cst_hash(ck), p.tab_slots), ck);
-                                        tab[j].P = (u32)tf[k];
-                                    }
-                                }
-                            }
-                            if (live) {
-                                if ((lane & ((G >> 2) - 1)) == 0 && (only < 0 || o == only)) invn[o * 32 + ri] = inv;
-                                if (sl == 0 && only <= 0) lenr[ri] = (L > 1) ? (L - 1) : 0;   // "length" = bigram count
-                            }
-                            if (live && sl == 0 && bad && only <= 0) ++bad_rows;
-                            __syncwarp();
-                            if (lane == 0) {
-                                __threadfence_block();               // this item's table entries before the count
-                                atomicAdd(&s_done_r, 1);
-                            }
-                        } else {
-                            // ---- phase C: score the row against the staged refs ----
-                            // There is no CTA barrier between the phases: a warp that ran out of reference
-                            // items has already done the table-independent half of this candidate item
-                            // above; here it waits until every reference item has been published.  Reference
-                            // items never wait on candidate items, so this cannot deadlock.
-                            if (MODE == CST_MODE_STAGED && !refs_ready) {
-                                // phase R was run once, by cst_refs_cook: wait for its image instead
-                                while (!mbar_try_wait(&s_img_bar, img_parity)) {}
-                                bad_image = hdr[0] != CST_IMG_MAGIC || hdr[1] != p.tab_slots ||
-                                            hdr[3] != (u32)p.use_eos;
-                                nref = bad_image ? 0 : (int)hdr[2];
-                                refs_ready = true;
-                            }
-                            if (MODE != CST_MODE_STAGED && !refs_ready) {
-                                if (lane == 0) {
-                                    const int np_r = (nref + 1) >> 1;
-                                    while (*reinterpret_cast<volatile int*>(&s_started[0]) < np_r) __nanosleep(32);
-                                    const int nlr = *reinterpret_cast<volatile int*>(&s_nlong[0]);
-                                    const int total_r = np_r + ((nlr * 2 <= nwarps) ? nlr * 4 : nlr);
-                                    while (*reinterpret_cast<volatile int*>(&s_done_r) < total_r) __nanosleep(32);
-                                }
-                                __syncwarp();
-                                refs_ready = true;
-                            }
-                            const int lenh = (L > 1) ? (L - 1) : 0;
-                            double* g = gh + (grp_shift(lane, G) & 16) * 2;
-                            for (int r = sl; r < nref; r += G)
-                                g[r] = s_gauss[lenh - lenr[r] + CST_GAUSS_HALF];
-                            __syncwarp();
-                            double num[4];
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                double inner = 0.0;
-                                if (lead[k]) {
-                                    const int idx = vid_find(tab, p.tab_slots, vid_home(h[k], p.tab_slots), key[k]);
-                                    if (idx >= 0) {
-                                        const u32 M = tab[idx].M;
-                                        u32 P = tab[idx].P & ~M;
-                                        const double* inv_k = invn + k * 32;
-                                        while (P) {            // refs holding the n-gram once: min(tf_h, 1) * 1
-                                            const int r = __ffs(P) - 1;
-                                            P &= P - 1u;
-                                            inner += inv_k[r] * g[r];
-                                        }
-                                        u32 Q = M;
-                                        while (Q) {            // refs holding it more than once: exact count
-                                            const int r = __ffs(Q) - 1;
-                                            Q &= Q - 1u;
-                                            const u64 ck = count_key((u32)idx, (u32)r);
-                                            const int j = vid_find(tab, p.tab_slots,
-                                                                   vid_home(cst_hash(ck), p.tab_slots), ck);
-                                            const int c = (int)tab[j].P;
-                                            const int m = (tf[k] < c ? tf[k] : c) * c;   // min(tf_h, tf_r) * tf_r
-                                            inner += (double)m * (inv_k[r] * g[r]);
-                                        }
-                                    }
-                                }
-                                num[k] = idf[k] * idf[k] * inner;
-                            }
-                            const double t = group_sum_orders(group_sum4_transposed(num, lane, G) * inv, G);
-                            __syncwarp();
-                            if (live && sl == 0) {
-                                if (G == 16) {
-                                    sc[ri] += t;
-                                } else if (split) {
-                                    part[4 * slot + only] = t;
-                                } else {
-                                    part[4 * slot] = t;
-                                    part[4 * slot + 1] = part[4 * slot + 2] = part[4 * slot + 3] = 0.0;
-                                }
-                                if (bad && c0 == r0 && only <= 0) ++bad_rows;
-                            }
-                        }
-                    }
-                }
-                if (MODE == CST_MODE_RAW && phase == 0) {   // no barrier here: see the wait in phase C
-                    CST_TICK(2);
-                    continue;
-                }
-                __syncthreads();
-                nl = s_nlong[phase];
-                if (!is_r && nl > 0) {
-                    for (int i = threadIdx.x; i < nl; i += blockDim.x)           // fixed order: deterministic
-                        sc[long_c[i]] += ((part[4 * i] + part[4 * i + 1]) + part[4 * i + 2]) + part[4 * i + 3];
-                    __syncthreads();                     // all probes done before the table is cleared again
-                }
-                CST_TICK(2 + phase);
-            }
-        }
-        if (MODE == CST_MODE_STAGED) {
-            // every thread observes the fetch (warps that had no candidate item have not yet) and takes
-            // the video's ref count from the image
-            while (!mbar_try_wait(&s_img_bar, img_parity)) {}
-            img_parity ^= 1u;
-            bad_image = hdr[0] != CST_IMG_MAGIC || hdr[1] != p.tab_slots || hdr[3] != (u32)p.use_eos;
-            R = bad_image ? 0 : (int)hdr[2];
-        }
-        if (R == 0) __syncthreads();                 // no chunk ran: order the zeroing of sc before phase B
-        if (bad_image && threadIdx.x == 0) ++bad_rows;
-        if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
-        if (MODE == CST_MODE_COOK) {
-            // cooking: what phase R left in shared memory (header, ref norms and lengths, table) is the
-            // video's image.  A video with no refs stages an empty table; one with more refs than a
-            // single pass holds cannot be staged and gets an invalid header (scores from it are NaN).
-            uint4* img = reinterpret_cast<uint4*>(hdr);
-            if (R == 0) {
-                for (u32 i = threadIdx.x; i < p.tab_slots + (u32)(CST_IMG_HEAD / 16); i += blockDim.x)
-                    img[i] = make_uint4(0, 0, 0, 0);
-                __syncthreads();
-            }
-            if (threadIdx.x == 0) {
-                if (R > p.chunk_refs && p.bad_out) atomicAdd(p.bad_out, 1u);
-                hdr[0] = (R <= p.chunk_refs) ? CST_IMG_MAGIC : 0u;
-                hdr[1] = p.tab_slots;
-                hdr[2] = (u32)R;
-                hdr[3] = (u32)p.use_eos;
-            }
-            __syncthreads();
-            uint4* out = reinterpret_cast<uint4*>(p.cook_out + (size_t)video * (size_t)p.cooked_stride);
-            for (u32 i = threadIdx.x; i < p.tab_slots + (u32)(CST_IMG_HEAD / 16); i += blockDim.x) out[i] = img[i];
-            __syncthreads();
-            continue;
-        }
-
-        // ---- phase B, spread over the whole CTA (a lone warp would hold 9 idle ones) ----
-        // scores: np.mean over the 4 orders, / len(refs), * 10  (compute_cider)
-        // (1 / R by reciprocal + multiply: a full double division is ~50 instructions of code
-        // in a kernel that is sensitive to its instruction footprint; the result differs from
-        // the reference's "/ len(refs)" by at most an ulp, the bar is 1e-5)
-        double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
-        if (bad_image) inv_R = __longlong_as_double(0x7ff8000000000000ll);   // not this build's image: NaN, loudly
-        for (int c = threadIdx.x; c < n_local; c += blockDim.x) {
-            const double s = (sc[c] * 0.25) * inv_R * 10.0;
-            sc[c] = s;
-            if (k_scores) {
-                const bool is_greedy = c >= p.cands_per_video;
-                const int64_t ci = video * p.cands_per_video + (is_greedy ? c - p.cands_per_video : c);
-                k_scores[(is_greedy ? p.n_cand : 0) + ci] = s;
-            }
-        }
-        __syncthreads();
-        if (k_mode >= 0) {
-            const int S = p.cands_per_video;
-            const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
-            const double* x = (k_mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
-            if (scb) {
-                // k lowest of the row (utils.py:294-312): element i is ranked by one warp with
-                // ballots (ties by index = stable sort); low[i] = x_i if its rank < k
-                for (int i = warp; i < S; i += nwarps) {
-                    const double xi = x[i];
-                    int rank = 0;
-                    for (int j0 = 0; j0 < S; j0 += 32) {
-                        const int j = j0 + lane;
-                        const double xj = (j < S) ? x[j] : 0.0;
-                        rank += __popc(__ballot_sync(CST_FULL, j < S && (xj < xi || (xj == xi && j < i))));
-                    }
-                    if (lane == 0) low[i] = (rank < p.scb_k) ? xi : 0.0;
-                }
-                __syncthreads();
-            }
-            double lowsum = 0.0;
-            if (scb) {
-                for (int i = lane; i < S; i += 32) lowsum += low[i];
-                lowsum = warp_sum(lowsum);                       // same fixed tree in every warp
-            }
-            const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
-            for (int i = threadIdx.x; i < S; i += blockDim.x) {
-                const double r = (k_mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
-                p.reward[video * S + i] = (float)r;
-            }
-            if (warp == 0) {                                      // the video's share of the statistics
-                double am = 0.0, ab = 0.0;
-                for (int i = lane; i < S; i += 32) {
-                    am += sc[i];
-                    if (k_mode == CST_BASE_GREEDY) ab += sc[S + i];
-                    if (k_mode == CST_BASE_SCB_GT) ab += x[i];
-                }
-                am = warp_sum(am);
-                ab = warp_sum(ab);
-                if (k_mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
-                if (lane == 0) {
-                    p.partials[2 * video] = am;
-                    p.partials[2 * video + 1] = ab;
-                }
-            }
-        }
-        __syncthreads();
-#ifdef CST_PHASE_TIMING
-        CST_TICK(4);
-        if (p.ctl && (threadIdx.x & 31) == 0) {      // per warp: where its time went (cycles, last chunk)
-            unsigned long long* t = reinterpret_cast<unsigned long long*>(p.ctl) + 8;
-            atomicAdd(t + 0, (unsigned long long)(tk[1] - tk[0]));
-            atomicAdd(t + 1, (unsigned long long)(tk[2] - tk[1]));
-            atomicAdd(t + 2, (unsigned long long)(tk[3] - tk[2]));
-            atomicAdd(t + 3, (unsigned long long)(tk[4] - tk[3]));
-            atomicAdd(t + 4, 1ull);
-        }
-#endif
-    }
-    if (k_mode >= 0 && !p.fold_apart) fold_stats_if_last(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats, red);
-}
+#include "cst_score2.cuh"
 
 // Standalone baseline over (n_groups, S) scores: one warp per group.
 __global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, const double* __restrict__ other,
@@ -1057,8 +604,6 @@ __global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, 
     }
     fold_stats_if_last(ctl, partials, n_groups, n_m, n_b, stats, red);
 }
-
-#include "cst_score2.cuh"
 
 // ---------------------------------------------------------------------------
 // host side of scoring
@@ -1090,129 +635,14 @@ static void stat_counts(int mode, int64_t n_cand, int seq_per_img, int k, double
     }
 }
 
-// every n-gram instance of the staged refs gets at most one slot (plus, for an n-gram repeated
-// inside a ref, one count slot paid for by the repeat itself); 25 % head-room keeps probes short
-static u32 table_slots_for(int chunk_refs, int ref_width) {
-    const u32 worst = (u32)chunk_refs * (u32)grams_per_row(ref_width);
-    const u32 slots = worst + worst / 4 + 8;
-    return slots < 64 ? 64 : slots;
-}
-
 extern "C" int64_t cst_refs_cooked_bytes(int32_t ref_width, int32_t refs_per_video) {
     if (ref_width < 1 || ref_width > CST_MAX_ROW_WIDTH || refs_per_video < 1 || refs_per_video > 32) return -1;
-    const int64_t raw = (int64_t)CST_IMG_HEAD + (int64_t)table_slots_for(refs_per_video, ref_width) * (int64_t)sizeof(VidSlot);
-    return (raw + 127) / 128 * 128;
-}
-
-template <int MODE, int CTAS, int BASE>
-static cudaError_t score_kernel_smem(size_t smem) {
-    return cudaFuncSetAttribute(k_score<MODE, CTAS, BASE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-}
-template <int MODE, int CTAS>
-static cudaError_t score_kernels_smem(size_t smem) {
-    cudaError_t e = score_kernel_smem<MODE, CTAS, CST_BASE_ANY>(smem);
-    if (CTAS == CST_MIN_CTAS) {
-        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_GREEDY>(smem);
-        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_SCB_GT>(smem);
-        if (e == cudaSuccess) e = score_kernel_smem<MODE, CST_MIN_CTAS, CST_BASE_SCB_SAMPLE>(smem);
-    }
-    return e;
-}
-
-// MODE raw / staged, full-occupancy build: pick the instantiation specialised for the baseline
-template <int MODE>
-static void launch_throughput(const ScoreParams& p, unsigned grid, int threads, size_t smem, cudaStream_t st) {
-    const bool plain = !p.scores && !p.ref_offsets && ((p.greedy != nullptr) == (p.mode == CST_BASE_GREEDY)) &&
-                       p.cand_esz == 4 && p.ref_esz == 4;
-    if (plain && p.mode == CST_BASE_SCB_SAMPLE)
-        k_score<MODE, CST_MIN_CTAS, CST_BASE_SCB_SAMPLE><<<grid, threads, smem, st>>>(p);
-    else if (plain && p.mode == CST_BASE_SCB_GT)
-        k_score<MODE, CST_MIN_CTAS, CST_BASE_SCB_GT><<<grid, threads, smem, st>>>(p);
-    else if (plain && p.mode == CST_BASE_GREEDY)
-        k_score<MODE, CST_MIN_CTAS, CST_BASE_GREEDY><<<grid, threads, smem, st>>>(p);
-    else
-        k_score<MODE, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
-}
-
-static int launch_score(const ScoreParams& p_in, int threads, size_t smem, cudaStream_t st, int rows_per_phase = 0) {
-    ScoreParams p = p_in;
-    static thread_local size_t configured[64] = {0};
-    static thread_local int n_sm[64] = {0};
-    int dev = 0;
-    CUDA_TRY(cudaGetDevice(&dev));
-    if (dev >= 64 || configured[dev] < smem) {
-        CUDA_TRY((score_kernels_smem<CST_MODE_RAW, CST_MIN_CTAS>(smem)));
-        CUDA_TRY((score_kernels_smem<CST_MODE_STAGED, CST_MIN_CTAS>(smem)));
-        CUDA_TRY((score_kernels_smem<CST_MODE_RAW, CST_SMALL_BATCH_CTAS>(smem)));
-        CUDA_TRY((score_kernels_smem<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS>(smem)));
-        CUDA_TRY((score_kernel_smem<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY>(smem)));
-        const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-        const int wide = (int)(smem + CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) - CST_SCORE_WORK_SMEM);
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_RAW, 1, CST_BASE_ANY, CST_WIDE_WARPS>, attr, wide));
-        CUDA_TRY(cudaFuncSetAttribute(k_score<CST_MODE_STAGED, 1, CST_BASE_ANY, CST_WIDE_WARPS>, attr, wide));
-        if (dev < 64) configured[dev] = smem;
-    }
-    int sms = 148;
-    if (dev < 64) {
-        if (!n_sm[dev]) CUDA_TRY(cudaDeviceGetAttribute(&n_sm[dev], cudaDevAttrMultiProcessorCount, dev));
-        sms = n_sm[dev];
-    }
-    const bool small = p.n_videos <= (int64_t)CST_SMALL_BATCH_CTAS * sms;
-    unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
-#ifdef CST_EXPERIMENT
-    if (const char* e = getenv("CST_EXP_GRID")) grid = (unsigned)atoi(e) < grid ? (unsigned)atoi(e) : grid;
-#endif
-    // a small batch with more than 20 rows in a phase (BASELINE config 3: 20 sampled + 20 greedy per
-    // video): one CTA of up to 20 warps per video does the phase in one round instead of two
-    const size_t wide_smem = smem + CST_SCORE_WORK_SMEM_W(CST_WIDE_WARPS) - CST_SCORE_WORK_SMEM;
-    if (small && !p.cook_out && rows_per_phase > 2 * CST_MAX_WARPS && p.n_videos <= sms && wide_smem <= 227 * 1024) {
-        int w = (rows_per_phase + 1) / 2;
-        if (w > CST_WIDE_WARPS) w = CST_WIDE_WARPS;
-        if (p.cooked)
-            k_score<CST_MODE_STAGED, 1, CST_BASE_ANY, CST_WIDE_WARPS><<<grid, w * 32, wide_smem, st>>>(p);
-        else
-            k_score<CST_MODE_RAW, 1, CST_BASE_ANY, CST_WIDE_WARPS><<<grid, w * 32, wide_smem, st>>>(p);
-        COUNT_LAUNCH();
-        CUDA_TRY(cudaGetLastError());
-        return CST_OK;
-    }
-    p.fold_apart = (p.mode >= 0 && !p.cook_out && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
-    if (p.cook_out)
-        k_score<CST_MODE_COOK, CST_MIN_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
-    else if (p.cooked && small)
-        k_score<CST_MODE_STAGED, CST_SMALL_BATCH_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
-    else if (p.cooked)
-        launch_throughput<CST_MODE_STAGED>(p, grid, threads, smem, st);
-    else if (small)
-        k_score<CST_MODE_RAW, CST_SMALL_BATCH_CTAS, CST_BASE_ANY><<<grid, threads, smem, st>>>(p);
-    else
-        launch_throughput<CST_MODE_RAW>(p, grid, threads, smem, st);
-    COUNT_LAUNCH();
-    CUDA_TRY(cudaGetLastError());
-    if (p.fold_apart) {
-        k_fold_stats<<<1, threads, 2 * (threads / 32) * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m,
-                                                                             p.n_b, p.stats);
-        COUNT_LAUNCH();
-        CUDA_TRY(cudaGetLastError());
-    }
-    return CST_OK;
-}
-
-// Which raw-row kernel serves a call: k_score2 (default) or, with CST_KERNEL=1 in the environment, the
-// round-1 kernel k_score (kept: staged references and cooking run on it, and the tests hold the two
-// against each other).
-static int raw_kernel_version() {
-    static const int v = [] {
-        const char* e = getenv("CST_KERNEL");
-        return (e && atoi(e) == 1) ? 1 : 2;
-    }();
-    return v;
+    return ((int64_t)CST2_IMG_BYTES + 127) / 128 * 128;       // one size: the table capacity is fixed
 }
 
 // cudaFuncAttributeMaxDynamicSharedMemorySize is per function and device, shared by all host threads:
 // remember the largest value set so far process-wide and only ever raise it.
 static std::mutex g_smem_mutex;
-static size_t g_smem_set2[64] = {0};
 static int g_sm_count[64] = {0};
 
 static int device_sms(int dev, int* sms) {
@@ -1224,6 +654,25 @@ static int device_sms(int dev, int* sms) {
     return CST_OK;
 }
 
+template <int MODE>
+static int launch_mode(const ScoreParams& p, unsigned grid, size_t smem, int dev, cudaStream_t st) {
+    {
+        static size_t set[64] = {0};                  // (one array per instantiation)
+        std::lock_guard<std::mutex> lock(g_smem_mutex);
+        if (dev < 0 || dev >= 64 || set[dev] < smem) {
+            CUDA_TRY(cudaFuncSetAttribute(k_score2<MODE, CST2_WARPS, CST2_CTAS>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (dev >= 0 && dev < 64) set[dev] = smem;
+        }
+    }
+    k_score2<MODE, CST2_WARPS, CST2_CTAS><<<grid, CST2_WARPS * 32, smem, st>>>(p);
+    COUNT_LAUNCH();
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+// One launch of the scoring kernel (raw rows, from staged images, or cooking images), plus the fold of
+// the statistics on large batches.
 static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     ScoreParams p = p_in;
     p.tab_slots = CST2_TAB_SLOTS;
@@ -1233,23 +682,19 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "scoring needs %zu bytes of shared memory per CTA", smem);
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
-    {
-        std::lock_guard<std::mutex> lock(g_smem_mutex);
-        if (dev < 0 || dev >= 64 || g_smem_set2[dev] < smem) {
-            CUDA_TRY(cudaFuncSetAttribute(k_score2<CST2_WARPS, CST2_CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)smem));
-            if (dev >= 0 && dev < 64) g_smem_set2[dev] = smem;
-        }
-    }
     int sms = 148;
     int rc = device_sms(dev, &sms);
     if (rc != CST_OK) return rc;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
-    p.fold_apart = (p.mode >= 0 && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
+    p.fold_apart = (p.mode >= 0 && !p.cook_out && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
     p.prefetch_ahead = sms * CST2_CTAS;
-    k_score2<CST2_WARPS, CST2_CTAS><<<grid, CST2_WARPS * 32, smem, st>>>(p);
-    COUNT_LAUNCH();
-    CUDA_TRY(cudaGetLastError());
+    if (p.cook_out)
+        rc = launch_mode<CST2_MODE_COOK>(p, grid, smem, dev, st);
+    else if (p.cooked)
+        rc = launch_mode<CST2_MODE_STAGED>(p, grid, smem, dev, st);
+    else
+        rc = launch_mode<CST2_MODE_RAW>(p, grid, smem, dev, st);
+    if (rc != CST_OK) return rc;
     if (p.fold_apart) {
         k_fold_stats<<<1, 256, 2 * 8 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);
         COUNT_LAUNCH();
@@ -1337,31 +782,10 @@ static int score_common(const char* who, const cst_df_table* t, const void* cand
         p.partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
         if (mode >= 0) stat_counts(mode, n_cand, cands_per_video, scb_k, p.n_m, p.n_b);
     }
-    // (k_score2 addresses rows with 32-bit pitches; a caller striding rows 4 GB apart gets k_score)
-    if (!cooked && raw_kernel_version() == 2 && (uint64_t)cand_stride * 8u < (1ull << 32) &&
-        (uint64_t)ref_stride * 8u < (1ull << 32))
-        return launch_score2(p, st);
-    // every n-gram instance of the staged refs gets at most one slot (plus, for an
-    // n-gram repeated inside a ref, one count slot paid for by the repeat itself)
-    p.tab_slots = table_slots_for(p.chunk_refs, ref_width);
-#ifdef CST_EXPERIMENT
-    if (const char* e = getenv("CST_EXP_SLOTS")) p.tab_slots = (u32)atoi(e);
-#endif
-
-    const int n_local = cands_per_video * (greedy ? 2 : 1);
-    int nwarps = ((p.chunk_refs > n_local ? p.chunk_refs : n_local) + 1) / 2;   // two rows per warp
-    if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
-    if (nwarps < 4) nwarps = 4;
-#ifdef CST_EXPERIMENT
-    if (const char* e = getenv("CST_EXP_WARPS")) nwarps = atoi(e);
-#endif
-    const size_t smem = CST_SCORE_FIXED_SMEM + (size_t)p.tab_slots * sizeof(VidSlot) +
-                        (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
-                        (size_t)4 * n_local * sizeof(double) + (size_t)n_local * sizeof(int);
-    if (smem > 227 * 1024) return fail(CST_E_RANGE, "%s: needs %zu bytes of shared memory per CTA", who, smem);
-
-    const int threads = nwarps * 32;
-    return launch_score(p, threads, smem, st, p.chunk_refs > n_local ? p.chunk_refs : n_local);
+    // (the kernel addresses rows with 32-bit pitches)
+    if ((uint64_t)cand_stride * 8u >= (1ull << 32) || (uint64_t)ref_stride * 8u >= (1ull << 32))
+        return fail(CST_E_RANGE, "%s: rows more than 4 GB apart", who);
+    return launch_score2(p, st);
 }
 
 extern "C" int cst_cider_scores(const cst_df_table* table, const void* cand, const void* greedy,
@@ -1516,14 +940,10 @@ extern "C" int cst_refs_cook(const cst_df_table* t, const void* refs, int32_t re
     p.use_eos = use_eos ? 1 : 0;
     p.mode = -1;
     p.bad_out = bad_rows_out;
-    p.tab_slots = table_slots_for(p.chunk_refs, ref_width);
     p.cook_out = reinterpret_cast<unsigned char*>(images_out);
     p.cooked_stride = image_stride;
-    int nwarps = (refs_per_video + 1) / 2;
-    if (nwarps > CST_MAX_WARPS) nwarps = CST_MAX_WARPS;
-    if (nwarps < 4) nwarps = 4;
-    const size_t smem = CST_SCORE_FIXED_SMEM + (size_t)p.tab_slots * sizeof(VidSlot);
-    return launch_score(p, nwarps * 32, smem, (cudaStream_t)stream);
+    if ((uint64_t)ref_stride * 8u >= (1ull << 32)) return fail(CST_E_RANGE, "%s: rows more than 4 GB apart", who);
+    return launch_score2(p, (cudaStream_t)stream);
 }
 
 // ---------------------------------------------------------------------------

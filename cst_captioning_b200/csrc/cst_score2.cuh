@@ -20,9 +20,14 @@
 //   sums     thread per (row, order): its list segment is contiguous, summed front to back ->
 //            norms, numerators.  No floating-point atomics, no shuffle trees: deterministic.
 //
-// Shared memory is a fixed 44 KB whatever the row widths and counts: a video whose references do
-// not fit the list (CST2_LIST_CAP instances) or need more than 32 presence bits is scored in several
-// reference chunks (CIDEr-D adds over references), candidates go through in batches likewise.
+// Shared memory is a fixed 44 KB whatever the row widths and counts.  References enter the video
+// table in sub-stages of at most CST2_LIST_CAP instances; a video with more than 32 references or
+// more than CST2_TAB_BUDGET instances is scored in several chunks, each with a table of its own
+// (CIDEr-D adds over references); candidates go through in batches likewise.
+//
+// Three instantiations of the one source (MODE): raw rows; COOK -- the reference half only, its
+// result (header, norms and lengths, table) written out as the video's image; STAGED -- that half
+// replaced by one bulk asynchronous copy of the image (cst_refs_cook / cst_reward_cooked).
 #pragma once
 
 #define CST2_ROWS 32                 /* rows per batch: presence bits of a chunk, lanes of the prefix scan */
@@ -33,6 +38,11 @@
 #ifndef CST2_TAB_SLOTS
 #define CST2_TAB_SLOTS 1531          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
 #endif
+#define CST2_TAB_BUDGET 1400         /* n-gram instances a table takes before a new chunk starts */
+#define CST2_MODE_RAW 0
+#define CST2_MODE_STAGED 1
+#define CST2_MODE_COOK 2
+#define CST2_IMG_MAGIC 0x43535432u   /* "CST2": layout version of a staged-reference image */
 #ifndef CST2_WARPS
 #define CST2_WARPS 8
 #endif
@@ -220,17 +230,20 @@ __device__ __forceinline__ u32 v2_insert(VidSlot* tab, u32 h, u64 key) {
         idx = v2_next<T>(idx, step);
     }
 }
-template <u32 T>
+// BOUNDED: the table came from a caller's buffer (a staged image): a damaged one may hold no free
+// slot on a probe path, so the walk gives up after T steps instead of spinning.
+template <u32 T, bool BOUNDED>
 __device__ __forceinline__ int v2_find(const VidSlot* tab, u32 h, u64 key) {
     u32 idx = vid_home(h, T);
     const u32 step = v2_step<T>(h);
 #pragma unroll 1
-    for (;;) {
+    for (u32 n = 0; !BOUNDED || n < T; ++n) {
         const u64 cur = tab[idx].key;
         if (cur == key) return (int)idx;
         if (cur == 0ull) return -1;
         idx = v2_next<T>(idx, step);
     }
+    return -1;
 }
 
 // One pass over the list: thread per slot.
@@ -238,9 +251,12 @@ __device__ __forceinline__ int v2_find(const VidSlot* tab, u32 h, u64 key) {
 //          synthetic key when the row holds the n-gram more than once), slot <- {(tf idf)^2, 0}
 //   else:  find it, walk the presence bits, slot <- {(tf idf)^2, idf^2 * sum_r min(tf_h, tf_r) tf_r inv_r g_r}
 // (Two slots per thread and round, so that their df-table loads travel together, was measured: slower.)
-template <int NT, u32 T>
+// row_off: references already in the table before this sub-stage (the presence bit of row r is
+// row_off + r)
+template <int NT, u32 T, bool BOUNDED>
 __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint4* list, int n_ent, int base1,
-                                           VidSlot* tab, const RefA* refA, const int* sL, const double* s_gauss) {
+                                           int row_off, VidSlot* tab, const RefA* refA, const int* sL,
+                                           const double* s_gauss) {
 #pragma unroll 1
     for (int i = (int)threadIdx.x; i < n_ent; i += NT) {
         const uint4 e = list[i];
@@ -267,16 +283,16 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
             if (idf != 0.0) {
                 if (is_r) {
                     const u32 idx = v2_insert<T>(tab, h, key);
-                    const u32 bit = 1u << row;
+                    const u32 bit = 1u << (row_off + row);
                     atomicOr(&tab[idx].P, bit);
                     if (tf > 1) {
                         atomicOr(&tab[idx].M, bit);
-                        const u64 ck = count_key(idx, (u32)row);
+                        const u64 ck = count_key(idx, (u32)(row_off + row));
                         const u32 j = v2_insert<T>(tab, cst_hash(ck), ck);
                         tab[j].P = (u32)tf;
                     }
                 } else {
-                    const int idx = v2_find<T>(tab, h, key);
+                    const int idx = v2_find<T, BOUNDED>(tab, h, key);
                     if (idx >= 0) {
                         const u32 M = tab[idx].M;
                         u32 P = tab[idx].P & ~M;
@@ -296,8 +312,8 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
                             const int r = __ffs(Q) - 1;
                             Q &= Q - 1u;
                             const u64 ck = count_key((u32)idx, (u32)r);
-                            const int j = v2_find<T>(tab, cst_hash(ck), ck);
-                            const int c = (int)tab[j].P;
+                            const int j = v2_find<T, BOUNDED>(tab, cst_hash(ck), ck);
+                            const int c = (j >= 0) ? (int)tab[j].P : 1;
                             const int m = (tf < c ? tf : c) * c;             // min(tf_h, tf_r) * tf_r
                             const RefA a = a_k[r];
                             inner += (double)m * (a.inv * s_gauss[lenh - a.len]);
@@ -312,13 +328,18 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
     }
 }
 
-// shared-memory layout: everything the hot loops touch sits at a compile-time offset
+// shared-memory layout: everything the hot loops touch sits at a compile-time offset.  The first
+// three pieces -- header, reference norms / lengths, table -- are what the reference stages of a
+// video leave behind: contiguous, so that a staged-reference image is one copy in either direction.
 #define CST2_CTOK_BYTES ((CST2_ROWS * CST2_TOK_STRIDE + 8) * sizeof(u16))
-#define CST2_OFF_LIST ((size_t)CST2_TAB_SLOTS * sizeof(VidSlot))
-#define CST2_OFF_REFA (CST2_OFF_LIST + (size_t)CST2_LIST_CAP * sizeof(uint4))
-#define CST2_OFF_CTOK (CST2_OFF_REFA + 4 * CST2_ROWS * sizeof(RefA))
+#define CST2_OFF_REFA ((size_t)16)                                   /* after hdr: magic, T, refs, use_eos */
+#define CST2_OFF_TAB (CST2_OFF_REFA + 4 * CST2_ROWS * sizeof(RefA))
+#define CST2_IMG_BYTES (CST2_OFF_TAB + (size_t)CST2_TAB_SLOTS * sizeof(VidSlot))
+#define CST2_OFF_LIST CST2_IMG_BYTES
+#define CST2_OFF_CTOK (CST2_OFF_LIST + (size_t)CST2_LIST_CAP * sizeof(uint4))
 #define CST2_OFF_SL (CST2_OFF_CTOK + CST2_CTOK_BYTES)
 #define CST2_OFF_SC (CST2_OFF_SL + CST2_ROWS * sizeof(int))
+static_assert(CST2_IMG_BYTES % 16 == 0 && CST2_OFF_TAB % 16 == 0, "the image must stay 16-byte aligned");
 
 // -DCST2_TIMING: cycles per warp and stage, added up in the scratch buffer (tools/phase_timing2.py;
 // the counters themselves cost time, read the numbers as proportions)
@@ -333,28 +354,32 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
 #define CST2_TICK(id)
 #endif
 
-// Stages of a video: a reference chunk (up to 32 rows / CST2_LIST_CAP instances), then every
-// candidate batch against it, then the next chunk if there is one.  Both kinds of stage run through
-// ONE copy of the code:   load + canonicalise | scan + emit | process   with a CTA barrier after
-// each; a reference stage ends with the norms of its rows, a candidate stage with the sums of its
+// Stages of a video.  A reference stage takes up to 32 rows / CST2_LIST_CAP instances into the video
+// table; further reference stages follow while the chunk has room (32 presence bits,
+// CST2_TAB_BUDGET instances).  Then every candidate batch meets the chunk, then the next chunk
+// starts on a cleared table, if the video has more references.  Both kinds of stage run through ONE
+// copy of the code:   load + canonicalise | scan + emit | process   with a CTA barrier after each;
+// a reference stage ends with the norms of its rows, a candidate stage with the sums of its
 // segments.  A video of the training shapes is one stage of each kind.
-template <int NW, int CTAS>
+template <int MODE, int NW, int CTAS>
 __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     constexpr int NT = NW * 32;
     constexpr u32 T = CST2_TAB_SLOTS;
     constexpr int PER = (CST2_ROWS + NW - 1) / NW;      // rows a warp canonicalises per batch
-    constexpr int budget = CST2_LIST_CAP;
+    constexpr bool STAGED = MODE == CST2_MODE_STAGED, COOK = MODE == CST2_MODE_COOK;
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double s_gauss[CST_GAUSS_N];
+    __shared__ unsigned long long s_img_bar;            // staged references: completion of the image fetch
     const int lane = threadIdx.x & 31;
     // (through a shuffle so that the compiler knows the value is the same in all lanes of the warp)
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
     const int n_local = S * (p.greedy ? 2 : 1);
 
-    VidSlot* tab = reinterpret_cast<VidSlot*>(smem);                          // [T]
-    uint4* list = reinterpret_cast<uint4*>(smem + CST2_OFF_LIST);             // [CST2_LIST_CAP]
+    u32* hdr = reinterpret_cast<u32*>(smem);                                  // [4]
     RefA* refA = reinterpret_cast<RefA*>(smem + CST2_OFF_REFA);               // [4][32]
+    VidSlot* tab = reinterpret_cast<VidSlot*>(smem + CST2_OFF_TAB);           // [T]
+    uint4* list = reinterpret_cast<uint4*>(smem + CST2_OFF_LIST);             // [CST2_LIST_CAP]
     u16* ctok = reinterpret_cast<u16*>(smem + CST2_OFF_CTOK);                 // [32][32] (+ tail pad)
     int* sL = reinterpret_cast<int*>(smem + CST2_OFF_SL);                     // [32] L | bad << 8 of the batch's rows
     double* sc = reinterpret_cast<double*>(smem + CST2_OFF_SC);               // [n_local]
@@ -365,18 +390,32 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     for (int i = threadIdx.x; i < CST_GAUSS_N; i += NT) s_gauss[i] = p.gauss[i];
     const u32 pitch_r = (u32)p.ref_stride * (u32)p.ref_esz;     // (the host checked that both fit 32 bits)
     const u32 pitch_c = (u32)p.cand_stride * (u32)p.cand_esz;
+    u32 img_parity = 0;
+    if (STAGED) {
+        if (threadIdx.x == 0) mbar_init(&s_img_bar, 1);
+        __syncthreads();
+    }
 
 #pragma unroll 1
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
-        int64_t r0, r1;
-        if (p.ref_offsets) {
-            r0 = p.ref_offsets[video];
-            r1 = p.ref_offsets[video + 1];
-        } else {
-            r0 = video * p.refs_per_video;
-            r1 = r0 + p.refs_per_video;
+        int64_t r0 = 0, r1 = 0;
+        if (!STAGED) {
+            if (p.ref_offsets) {
+                r0 = p.ref_offsets[video];
+                r1 = p.ref_offsets[video + 1];
+            } else {
+                r0 = video * p.refs_per_video;
+                r1 = r0 + p.refs_per_video;
+            }
         }
-        const int R = (int)(r1 - r0);
+        int R = (int)(r1 - r0);
+        bool bad_image = false;
+        if (STAGED && threadIdx.x == 0) {
+            // one bulk copy by the copy engine: header, norms / lengths and table land while the warps
+            // load and canonicalise the candidates; the wait is just before the table's first use
+            const int64_t img = p.cooked_index ? p.cooked_index[video] : video;
+            bulk_fetch(hdr, p.cooked + (size_t)img * (size_t)p.cooked_stride, (u32)CST2_IMG_BYTES, &s_img_bar);
+        }
 #if CST2_PREFETCH
         // CTAs start in blockIdx order, so the video `prefetch_ahead` (= resident CTAs) further on is
         // the one a CTA will start on about when this one ends: pull its rows into L2 now, and that
@@ -384,13 +423,18 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
         if (threadIdx.x == 0 && !p.ref_offsets) {
             const int64_t v2 = video + p.prefetch_ahead;
             if (v2 < p.n_videos) {
-                const char* a = reinterpret_cast<const char*>(p.refs) + (size_t)(v2 * p.refs_per_video) * pitch_r;
-                const char* b = reinterpret_cast<const char*>(p.cand) + (size_t)(v2 * S) * pitch_c;
-                const u32 na = ((u32)p.refs_per_video * pitch_r) & ~15u, nb = ((u32)S * pitch_c) & ~15u;
-                if (na && !(reinterpret_cast<uintptr_t>(a) & 15u))
-                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"(na) : "memory");
-                if (nb && !(reinterpret_cast<uintptr_t>(b) & 15u))
-                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b), "r"(nb) : "memory");
+                if (!STAGED) {
+                    const char* a = reinterpret_cast<const char*>(p.refs) + (size_t)(v2 * p.refs_per_video) * pitch_r;
+                    const u32 na = ((u32)p.refs_per_video * pitch_r) & ~15u;
+                    if (na && !(reinterpret_cast<uintptr_t>(a) & 15u))
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"(na) : "memory");
+                }
+                if (!COOK) {
+                    const char* b = reinterpret_cast<const char*>(p.cand) + (size_t)(v2 * S) * pitch_c;
+                    const u32 nb = ((u32)S * pitch_c) & ~15u;
+                    if (nb && !(reinterpret_cast<uintptr_t>(b) & 15u))
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b), "r"(nb) : "memory");
+                }
             }
         }
 #endif
@@ -404,14 +448,18 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
         u32 bad_rows = 0;
 
         int64_t rbase = r0;
-        int cb = -1;                    // < 0: the stage is the reference chunk at rbase; else candidate row cb
-        int nref = 0;
+        int cb = STAGED ? 0 : -1;       // < 0: the stage takes references from rbase on; else candidates from row cb
+        int chunk_rows = 0, chunk_inst = 0;              // references / instances in the table so far
+        bool img_ready = !STAGED;
+        bool first_chunk = true;
+        bool more = STAGED ? n_local > 0 : rbase < r1;
 #pragma unroll 1
-        while (rbase < r1) {
-            const bool is_r = cb < 0;
+        while (more) {
+            const bool is_r = COOK || (!STAGED && cb < 0);
             // ---- load + canonicalise the stage's rows: warp w takes rows w, w + NW, ...; all loads are
             // issued before any is used ----
-            const int n_try = is_r ? (int)((r1 - rbase) < CST2_ROWS ? (r1 - rbase) : CST2_ROWS)
+            const int room = CST2_ROWS - chunk_rows;
+            const int n_try = is_r ? (int)((r1 - rbase) < room ? (r1 - rbase) : room)
                                    : ((n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS);
             {
                 const int esz = is_r ? p.ref_esz : p.cand_esz;
@@ -444,7 +492,7 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
                     }
                     u[j] = v;
                 }
-                if (is_r) {
+                if (!STAGED && is_r && chunk_rows == 0) {                    // a new chunk: empty table
                     uint4* z = reinterpret_cast<uint4*>(tab);
 #pragma unroll 2
                     for (u32 i = threadIdx.x; i < T; i += NT) z[i] = make_uint4(0, 0, 0, 0);
@@ -461,11 +509,12 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             CST2_TICK(is_r ? 0 : 6);
             __syncthreads();
             CST2_TICK(is_r ? 1 : 7);
-            // ---- scan + emit ----
-            const V2Scan sb = v2_scan(sL, n_try, budget, lane);
+            // ---- scan + emit (the budgets leave room for one row of 32 tokens: at least one row fits) ----
+            const int left = CST2_TAB_BUDGET - chunk_inst;
+            const V2Scan sb = v2_scan(sL, n_try, (is_r && left < CST2_LIST_CAP) ? left : CST2_LIST_CAP, lane);
             const int nfit = sb.nfit;
             // rows with ids outside [-1, 65534]: every reference row once, candidates in the first chunk
-            if (warp == 0 && lane < nfit && (is_r || rbase == r0)) bad_rows += (u32)(sL[lane] >> 8);
+            if (warp == 0 && lane < nfit && (is_r || first_chunk)) bad_rows += (u32)(sL[lane] >> 8);
 #pragma unroll 1
             for (int pair = warp; 2 * pair < nfit; pair += NW) {
                 const int ra = 2 * pair, rb = ra + 1;
@@ -485,8 +534,18 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             CST2_TICK(is_r ? 2 : 8);
             __syncthreads();
             CST2_TICK(is_r ? 3 : 9);
+            if (STAGED && !img_ready) {
+                // the reference half was run once, by cst_refs_cook: its image must have landed by now
+                while (!mbar_try_wait(&s_img_bar, img_parity)) {}
+                img_parity ^= 1u;
+                img_ready = true;
+                bad_image = hdr[0] != CST2_IMG_MAGIC || hdr[1] != T || hdr[3] != (u32)p.use_eos || hdr[2] > 32u;
+                R = bad_image ? 0 : (int)hdr[2];
+                chunk_rows = R;
+            }
             // ---- process ----
-            v2_process<NT, T>(p, is_r, list, sb.n_ent, sb.base1, tab, refA, sL, s_gauss);
+            if (!(STAGED && bad_image))
+                v2_process<NT, T, STAGED>(p, is_r, list, sb.n_ent, sb.base1, chunk_rows, tab, refA, sL, s_gauss);
             CST2_TICK(is_r ? 4 : 10);
             __syncthreads();
             CST2_TICK(is_r ? 5 : 11);
@@ -516,7 +575,7 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
                         ra.inv = inv;
                         ra.len = (L > 1) ? L - 1 : 0;                        // "length" = bigram count
                         ra.pad = 0;
-                        refA[k * CST2_ROWS + row] = ra;
+                        refA[k * CST2_ROWS + chunk_rows + row] = ra;
                     }
                 } else {
                     double val = b * inv;
@@ -527,22 +586,63 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             }
             CST2_TICK(12);
             if (is_r) {
-                nref = nfit;
-                cb = 0;
+                chunk_rows += nfit;
+                chunk_inst += sb.n_ent;
+                rbase += nfit;
+                // another reference stage into the same table while a row of any length still fits
+                if (!(rbase < r1 && chunk_rows < CST2_ROWS && CST2_TAB_BUDGET - chunk_inst >= 4 * 32 - 6)) {
+                    if (COOK) more = false;         // the image holds ONE chunk (the host checks rbase == r1)
+                    cb = 0;
+                }
             } else {
                 cb += nfit;
-                if (cb >= n_local) {    // the chunk has met every candidate: next chunk, if any
-                    rbase += nref;
+                if (cb >= n_local) {                // the chunk has met every candidate: next chunk, if any
+                    more = !STAGED && rbase < r1;
                     cb = -1;
+                    chunk_rows = 0;
+                    chunk_inst = 0;
+                    first_chunk = false;
                 }
             }
         }
+        if (STAGED && !img_ready) {                 // (no candidate stage ran: still take the fetch off the barrier)
+            while (!mbar_try_wait(&s_img_bar, img_parity)) {}
+            img_parity ^= 1u;
+        }
+        if (COOK) {
+            // what the reference stages left in shared memory is the video's image.  A video whose
+            // references did not fit one chunk cannot be staged: invalid header (scores from it are NaN).
+            __syncthreads();
+            const bool fits = rbase >= r1;
+            if (R == 0) {                           // no references: an empty table
+                uint4* z = reinterpret_cast<uint4*>(tab);
+#pragma unroll 1
+                for (u32 i = threadIdx.x; i < T; i += NT) z[i] = make_uint4(0, 0, 0, 0);
+            }
+            if (threadIdx.x == 0) {
+                if (!fits) ++bad_rows;
+                hdr[0] = fits ? CST2_IMG_MAGIC : 0u;
+                hdr[1] = T;
+                hdr[2] = (u32)R;
+                hdr[3] = (u32)p.use_eos;
+            }
+            if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+            __syncthreads();
+            const uint4* img = reinterpret_cast<const uint4*>(smem);
+            uint4* out = reinterpret_cast<uint4*>(p.cook_out + (size_t)video * (size_t)p.cooked_stride);
+#pragma unroll 1
+            for (u32 i = threadIdx.x; i < (u32)(CST2_IMG_BYTES / 16); i += NT) out[i] = img[i];
+            __syncthreads();
+            continue;
+        }
+        if (STAGED && bad_image && threadIdx.x == 0) ++bad_rows;
         if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
         __syncthreads();
 
         // ---- scores, baseline (utils.py:292-322), rewards, per-video statistics ----
         // np.mean over the 4 orders, / len(refs), * 10 (compute_cider)
-        const double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
+        double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
+        if (STAGED && bad_image) inv_R = __longlong_as_double(0x7ff8000000000000ll);   // not this build's image: NaN, loudly
         const int k_mode = p.mode;
 #pragma unroll 1
         for (int c = threadIdx.x; c < n_local; c += NT) {
@@ -620,8 +720,6 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
 }
 
 static size_t score2_smem(int n_local, int cands_per_video, int nwarps) {
-    return (size_t)CST2_TAB_SLOTS * sizeof(VidSlot) + (size_t)CST2_LIST_CAP * sizeof(uint4) +
-           4 * CST2_ROWS * sizeof(RefA) + CST2_CTOK_BYTES +
-           CST2_ROWS * sizeof(int) + (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
+    return CST2_OFF_SC + (size_t)n_local * sizeof(double) + (size_t)cands_per_video * sizeof(double) +
            2 * (size_t)nwarps * sizeof(double);
 }
