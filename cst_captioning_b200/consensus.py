@@ -8,9 +8,14 @@ frequency is recomputed from the references of that very call and
 what the data loader later hands to the reward path as ``bcmrscores``
 (``dataloader.py:66-73, 142-144``) for the SCB baseline and the WXE weights.
 
-Here each of the ``seq_per_img`` passes builds its corpus-mode df table on the device
-(``DfTable.from_rows``) and scores column i against the rest with the same fused kernel
-as the RL path.
+The twenty corpus-mode tables differ from the df of ALL captions only where caption i is a
+video's sole holder of an n-gram: ``df_i(g) = df_all(g) - #{videos whose caption i alone holds
+g}``.  So the table is built ONCE from all rows, one more pass over the rows counts the sole holders
+per (caption, n-gram) (``cst_df_sole_holders``), and pass i switches the table's idf to
+``log V - log max(1, df_all - excl_i)`` with one streaming kernel (``cst_df_leave_one_out``) before
+scoring column i against the rest with the same fused kernel as the RL path.  Videos whose captions
+exceed one shared-memory table (more than 32 captions or 1,400 n-gram instances) fall back to one
+device-built table per pass.
 
 Difference in input, not in arithmetic: the reference scores the raw caption *words*
 of the cocofmt json, this module scores token-id rows.  They agree when the rows hold
@@ -21,8 +26,9 @@ from __future__ import annotations
 
 import torch
 
+from ._lib import lib, check
 from .ciderd import CiderD
-from .df_table import DfTable
+from .df_table import DfTable, _row_dtype
 from .reward import RefSet
 
 
@@ -38,21 +44,42 @@ def consensus_scores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0):
         raise ValueError('seq_per_img must lie in [1, refs per video]')
     if remove_in_ref and n_refs < 2:
         raise ValueError('remove_in_ref needs at least two captions per video')
-    out = torch.empty(n_videos, seq_per_img, dtype=torch.float64, device=refs.device)
-    shared = None
-    if not remove_in_ref:                       # one corpus, one table for every pass
-        shared = (CiderD(df=DfTable.from_rows(refs, use_eos=use_eos)),
-                  RefSet(refs.reshape(n_videos * n_refs, width), per_video=n_refs))
-    for i in range(seq_per_img):
-        if remove_in_ref:                       # compute_scores.py:86-87
-            others = torch.cat([refs[:, :i], refs[:, i + 1:]], dim=1).contiguous()
-            scorer = CiderD(df=DfTable.from_rows(others, use_eos=use_eos))
-            refset = RefSet(others.reshape(n_videos * (n_refs - 1), width), per_video=n_refs - 1)
-        else:
-            scorer, refset = shared
-        hyp = refs[:, i].contiguous()
-        out[:, i] = scorer.score_rows(hyp, refset, 1, use_eos=use_eos)
-        if remove_in_ref:
-            torch.cuda.current_stream(refs.device).synchronize()   # table is freed with `scorer`
-            scorer.table.close()
+    refs = refs.contiguous()
+    dev = refs.device
+    out = torch.empty(n_videos, seq_per_img, dtype=torch.float64, device=dev)
+    if n_videos == 0:
+        return out
+    table = DfTable.from_rows(refs, use_eos=use_eos)          # df of ALL captions, ref_len = log(videos)
+    scorer = CiderD(df=table)
+    flat = refs.reshape(n_videos * n_refs, width)
+    if not remove_in_ref:                                     # one corpus for every pass
+        refset = RefSet(flat, per_video=n_refs)
+        for i in range(seq_per_img):
+            out[:, i] = scorer.score_rows(refs[:, i], refset, 1, use_eos=use_eos)
+        torch.cuda.current_stream(dev).synchronize()
+        table.close()
+        return out
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    excl = None
+    if n_refs <= 32:
+        excl = torch.zeros((n_refs, table.capacity), dtype=torch.int32, device=dev)
+        too_large = torch.zeros(1, dtype=torch.int32, device=dev)
+        check(lib.cst_df_sole_holders(table.handle, flat.data_ptr(), _row_dtype(flat), flat.shape[0], width,
+                                      flat.stride(0), n_refs, n_videos, int(use_eos), excl.data_ptr(),
+                                      too_large.data_ptr(), stream))
+        if int(too_large.item()) != 0:
+            excl = None
+    for i in range(seq_per_img):                              # compute_scores.py:81-92
+        others = torch.cat([refs[:, :i], refs[:, i + 1:]], dim=1).contiguous()
+        refset = RefSet(others.reshape(n_videos * (n_refs - 1), width), per_video=n_refs - 1)
+        if excl is not None:
+            check(lib.cst_df_leave_one_out(table.handle, excl.data_ptr(), i, stream))
+            out[:, i] = scorer.score_rows(refs[:, i], refset, 1, use_eos=use_eos)
+        else:                                                 # a table of its own for this pass
+            t_i = DfTable.from_rows(others, use_eos=use_eos)
+            out[:, i] = CiderD(df=t_i).score_rows(refs[:, i].contiguous(), refset, 1, use_eos=use_eos)
+            torch.cuda.current_stream(dev).synchronize()
+            t_i.close()
+    torch.cuda.current_stream(dev).synchronize()              # the table is freed with `scorer`
+    table.close()
     return out

@@ -579,6 +579,8 @@ struct ScoreParams {
     int fold_apart;                 // the statistics are folded by k_fold_stats after this launch
     u32 list_cap;                   // k_score2: n-gram instances per batch (shared-memory list)
     int prefetch_ahead;             // k_score2: how many videos ahead a CTA prefetches rows into L2
+    u32* excl;                      // leave-one-out counts [caption][df slot] (CST2_MODE_EXCL)
+    size_t excl_stride;             // = df slots
 };
 
 #ifndef CST_FOLD_APART_CTAS
@@ -686,9 +688,11 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     int rc = device_sms(dev, &sms);
     if (rc != CST_OK) return rc;
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
-    p.fold_apart = (p.mode >= 0 && !p.cook_out && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
+    p.fold_apart = (p.mode >= 0 && !p.cook_out && !p.excl && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
     p.prefetch_ahead = sms * CST2_CTAS;
-    if (p.cook_out)
+    if (p.excl)
+        rc = launch_mode<CST2_MODE_EXCL>(p, grid, smem, dev, st);
+    else if (p.cook_out)
         rc = launch_mode<CST2_MODE_COOK>(p, grid, smem, dev, st);
     else if (p.cooked)
         rc = launch_mode<CST2_MODE_STAGED>(p, grid, smem, dev, st);
@@ -944,6 +948,72 @@ extern "C" int cst_refs_cook(const cst_df_table* t, const void* refs, int32_t re
     p.cooked_stride = image_stride;
     if ((uint64_t)ref_stride * 8u >= (1ull << 32)) return fail(CST_E_RANGE, "%s: rows more than 4 GB apart", who);
     return launch_score2(p, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------
+// leave-one-out document frequencies (the corpus-mode df of compute_scores.py:81-92)
+// ---------------------------------------------------------------------------
+// excl_out[i * slots + s] += number of videos in which caption i is the only one holding the n-gram of
+// df slot s (slots = cst_df_capacity).  The table must have been built from these very rows.
+extern "C" int cst_df_sole_holders(const cst_df_table* t, const void* rows, int32_t dtype, int64_t n_rows,
+                                   int32_t width, int64_t stride, int32_t per_video, int64_t n_videos,
+                                   int32_t use_eos, uint32_t* excl_out, uint32_t* too_large_out, void* stream) {
+    const char* who = "cst_df_sole_holders";
+    if (!t) return fail(CST_E_ARG, "%s: table is NULL", who);
+    if (n_videos < 0 || n_rows != n_videos * (int64_t)per_video) return fail(CST_E_ARG, "%s: bad sizes", who);
+    if (per_video < 1 || per_video > 32) return fail(CST_E_RANGE, "%s: 1..32 captions per video (got %d)", who, per_video);
+    if (width < 1 || width > CST_MAX_ROW_WIDTH) return fail(CST_E_RANGE, "%s: row width %d outside [1, %d]", who, width, CST_MAX_ROW_WIDTH);
+    if (stride < width || (uint64_t)stride * 8u >= (1ull << 32)) return fail(CST_E_ARG, "%s: bad stride", who);
+    if (!dtype_bytes(dtype)) return fail(CST_E_ARG, "%s: bad dtype", who);
+    if (n_videos == 0) return CST_OK;
+    if (!rows || !excl_out) return fail(CST_E_ARG, "%s: NULL argument", who);
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "%s: cannot select device %d", who, t->device);
+    ScoreParams p;
+    memset(&p, 0, sizeof(p));
+    p.df = view_of(t);
+    p.gauss = t->gauss;
+    p.refs = rows;
+    p.ref_esz = dtype_bytes(dtype);
+    p.cand_esz = p.ref_esz;
+    p.ref_width = width;
+    p.cand_width = 1;
+    p.ref_stride = stride;
+    p.refs_per_video = per_video;
+    p.chunk_refs = per_video;
+    p.n_videos = n_videos;
+    p.use_eos = use_eos ? 1 : 0;
+    p.mode = -1;
+    p.bad_out = too_large_out;
+    p.excl = excl_out;
+    p.excl_stride = (size_t)t->n_buckets * CST_BUCKET;
+    return launch_score2(p, (cudaStream_t)stream);
+}
+
+// idf of every stored n-gram for the pass that leaves caption `caption` out:
+// idfv[s] = lut[df[s] - excl[caption][s]], and the unigram shortcut array follows
+__global__ void k_fill_idf_loo(const u64* __restrict__ keys, const u32* __restrict__ dfc, const u32* __restrict__ excl,
+                               const double* __restrict__ lut, double* idfv, double* uni, size_t slots) {
+    const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= slots) return;
+    const u64 key = keys[s];
+    if (key == 0ull) return;
+    const u32 d = dfc[s] - excl[s];
+    const double w = lut[d];
+    idfv[s] = w;
+    if ((key >> 16) == 0ull && (u32)key - 1u < CST_UNI_N) uni[(u32)key - 1u] = w;
+}
+
+extern "C" int cst_df_leave_one_out(cst_df_table* t, const uint32_t* excl, int32_t caption, void* stream) {
+    if (!t || !excl || caption < 0) return fail(CST_E_ARG, "cst_df_leave_one_out: bad argument");
+    DeviceGuard guard(t->device);
+    if (!guard.ok) return fail(CST_E_CUDA, "cst_df_leave_one_out: cannot select device %d", t->device);
+    const size_t slots = (size_t)t->n_buckets * CST_BUCKET;
+    k_fill_idf_loo<<<(unsigned)((slots + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        t->keys, t->dfc, excl + (size_t)caption * slots, t->lut, t->idfv, t->uni, slots);
+    COUNT_LAUNCH();
+    CUDA_TRY(cudaGetLastError());
+    return CST_OK;
 }
 
 // ---------------------------------------------------------------------------

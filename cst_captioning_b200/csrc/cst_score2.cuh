@@ -42,6 +42,7 @@
 #define CST2_MODE_RAW 0
 #define CST2_MODE_STAGED 1
 #define CST2_MODE_COOK 2
+#define CST2_MODE_EXCL 3    /* leave-one-out document frequencies (compute_scores.py:81-92), see k_score2 */
 #define CST2_IMG_MAGIC 0x43535432u   /* "CST2": layout version of a staged-reference image */
 #ifndef CST2_WARPS
 #define CST2_WARPS 8
@@ -252,8 +253,8 @@ __device__ __forceinline__ int v2_find(const VidSlot* tab, u32 h, u64 key) {
 //   else:  find it, walk the presence bits, slot <- {(tf idf)^2, idf^2 * sum_r min(tf_h, tf_r) tf_r inv_r g_r}
 // (Two slots per thread and round, so that their df-table loads travel together, was measured: slower.)
 // row_off: references already in the table before this sub-stage (the presence bit of row r is
-// row_off + r)
-template <int NT, u32 T, bool BOUNDED>
+// row_off + r).  EXCL: every n-gram is published, with its slot in the df table in the M field.
+template <int NT, u32 T, bool BOUNDED, bool EXCL>
 __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint4* list, int n_ent, int base1,
                                            int row_off, VidSlot* tab, const RefA* refA, const int* sL,
                                            const double* s_gauss) {
@@ -268,19 +269,24 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
             const int tf = (int)(e.z >> 8);
             const u32 h = cst_hash(key);
             double idf;
-            if (i < base1) {                                   // unigram: token codes are 1 .. 65535
+            int slot = -1;
+            if (!EXCL && i < base1) {                          // unigram: token codes are 1 .. 65535
                 idf = __ldg(p.df.uni + (e.x - 1u));
             } else {
                 u64 kk[4];
                 const u32 b = cst_slot(h, p.df.n_buckets);
                 ld_bucket(p.df.keys + (size_t)b * CST_BUCKET, kk);
-                const int slot = v2_resolve(p.df, key, b, kk);
+                slot = v2_resolve(p.df, key, b, kk);
                 idf = (slot >= 0) ? __ldg(p.df.idfv + slot) : p.df.unseen;
             }
             const double w = (double)tf * idf;                 // counts2vec: vec = tf * idf
             w2 = w * w;                                        // norm += vec ** 2
             // an n-gram every document holds has idf = 0: exact zeros on both sides, no table entry
-            if (idf != 0.0) {
+            if (EXCL) {
+                const u32 idx = v2_insert<T>(tab, h, key);
+                atomicOr(&tab[idx].P, 1u << (row_off + row));
+                tab[idx].M = (u32)(slot + 1);                  // (every holder stores the same value)
+            } else if (idf != 0.0) {
                 if (is_r) {
                     const u32 idx = v2_insert<T>(tab, h, key);
                     const u32 bit = 1u << (row_off + row);
@@ -366,7 +372,8 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     constexpr int NT = NW * 32;
     constexpr u32 T = CST2_TAB_SLOTS;
     constexpr int PER = (CST2_ROWS + NW - 1) / NW;      // rows a warp canonicalises per batch
-    constexpr bool STAGED = MODE == CST2_MODE_STAGED, COOK = MODE == CST2_MODE_COOK;
+    constexpr bool STAGED = MODE == CST2_MODE_STAGED, EXCL = MODE == CST2_MODE_EXCL;
+    constexpr bool COOK = MODE == CST2_MODE_COOK || EXCL;      // reference stages only
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ double s_gauss[CST_GAUSS_N];
     __shared__ unsigned long long s_img_bar;            // staged references: completion of the image fetch
@@ -545,7 +552,7 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             }
             // ---- process ----
             if (!(STAGED && bad_image))
-                v2_process<NT, T, STAGED>(p, is_r, list, sb.n_ent, sb.base1, chunk_rows, tab, refA, sL, s_gauss);
+                v2_process<NT, T, STAGED, EXCL>(p, is_r, list, sb.n_ent, sb.base1, chunk_rows, tab, refA, sL, s_gauss);
             CST2_TICK(is_r ? 4 : 10);
             __syncthreads();
             CST2_TICK(is_r ? 5 : 11);
@@ -608,6 +615,26 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
         if (STAGED && !img_ready) {                 // (no candidate stage ran: still take the fetch off the barrier)
             while (!mbar_try_wait(&s_img_bar, img_parity)) {}
             img_parity ^= 1u;
+        }
+        if (EXCL) {
+            // Leave-one-out document frequencies.  compute_scores.py:81-92 scores caption i of every video
+            // against the others with a df recomputed WITHOUT caption i; that df differs from the df of
+            // all captions only where caption i is the video's sole holder of an n-gram:
+            //     df_i(g) = df_all(g) - #{videos whose caption i alone holds g}.
+            // The table knows the holders of each n-gram (P): count the sole ones, per (caption, df slot).
+            __syncthreads();
+            if (rbase < r1) {                       // more captions than one table takes: the caller falls back
+                if (threadIdx.x == 0 && p.bad_out) atomicAdd(p.bad_out, 1u);
+            } else {
+#pragma unroll 1
+                for (u32 i = threadIdx.x; i < T; i += NT) {
+                    const u32 P = tab[i].P, g = tab[i].M;
+                    if (tab[i].key != 0ull && g != 0u && (P & (P - 1u)) == 0u)
+                        atomicAdd(p.excl + (size_t)(__ffs(P) - 1) * p.excl_stride + (g - 1u), 1u);
+                }
+            }
+            __syncthreads();
+            continue;
         }
         if (COOK) {
             // what the reference stages left in shared memory is the video's image.  A video whose

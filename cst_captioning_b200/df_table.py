@@ -119,6 +119,9 @@ class DfTable:
         elif video_offsets is None:
             raise ValueError('video_offsets is required for 2-D rows')
         rows = rows.contiguous()
+        # the build runs on the legacy default stream and is synchronous: whatever produced `rows` on
+        # the caller's (possibly non-blocking) stream has to be done first
+        torch.cuda.current_stream(rows.device).synchronize()
         dtype = _row_dtype(rows)
         off = np.ascontiguousarray(video_offsets, dtype=np.int64)
         n_videos = len(off) - 1

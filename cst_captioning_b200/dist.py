@@ -59,6 +59,8 @@ def get_cst_reward_sharded(model_res, data_gts, bcmr_scorer, bcmrscores=None, se
     """``get_cst_reward`` on this rank's slice of a replicated global batch.
 
     -> (local rewards (n_local, T), global m_score, global b_score, (lo, hi) videos).
+    A rank whose slice is empty (more ranks than videos in a short last batch) contributes zero
+    statistics and still takes part in the all-reduce.
     Callers that already hold only their own slice call ``get_cst_reward(...,
     return_stats=True)`` and ``all_reduce_stats`` directly (that is what bench.py does).
     """

@@ -51,8 +51,9 @@ class HostRewardPipeline:
                                                                 device=self.device),
                         'bcmr': torch.empty((per, self.seq_per_img), dtype=torch.float64, device=self.device)
                         if bcmr is not None else None,
-                        'uploaded': torch.cuda.Event(), 'consumed': torch.cuda.Event(), 'used': False}
-            self._bufs = (key, [mk(), mk()])
+                        'uploaded': torch.cuda.Event(), 'consumed': torch.cuda.Event(),
+                        'scored': torch.cuda.Event(), 'used': False}
+            self._bufs = (key, [mk(), mk()], torch.zeros(_lib.N_STATS, dtype=torch.float64, device=self.device))
         return self._bufs[1]
 
     def __call__(self, sampled, refs, bcmrscores=None, out=None):
@@ -68,11 +69,14 @@ class HostRewardPipeline:
             raise ValueError('sampled must hold seq_per_img rows per video')
         if out is None:
             out = torch.empty(sampled.shape[0], dtype=torch.float32).pin_memory()
+        if n_videos == 0:                                # an empty shard: nothing to score, zero statistics
+            return out, torch.zeros(_lib.N_STATS, dtype=torch.float64, device=self.device)
         per = (n_videos + self.slices - 1) // self.slices
         bufs = self._buffers(sampled, refs, bcmrscores, per)
         main = torch.cuda.current_stream(self.device)
         self.copy_stream.wait_stream(main)
-        total = torch.zeros(_lib.N_STATS, dtype=torch.float64, device=self.device)
+        total = self._bufs[2]
+        total.zero_()
         done = []
         for i, lo in enumerate(range(0, n_videos, per)):
             hi = min(n_videos, lo + per)
@@ -97,10 +101,9 @@ class HostRewardPipeline:
             total += stats
             b['consumed'].record(main)
             b['used'] = True
-            ready = torch.cuda.Event()
-            ready.record(main)
+            b['scored'].record(main)
             with torch.cuda.stream(self.out_stream):
-                self.out_stream.wait_event(ready)
+                self.out_stream.wait_event(b['scored'])
                 out[lo * s:hi * s].copy_(rew[:, 0], non_blocking=True)
                 rew.record_stream(self.out_stream)
             done.append(rew)
@@ -110,4 +113,4 @@ class HostRewardPipeline:
         for b in bufs:
             b['used'] = False
         main.wait_stream(self.copy_stream)
-        return out, total
+        return out, total.clone()

@@ -40,7 +40,7 @@ class RefSet:
             rows = rows.contiguous()
         self.rows = rows
         if offsets is None:
-            if not per_video or rows.shape[0] % per_video:
+            if not per_video or per_video < 1 or rows.shape[0] % per_video:
                 raise ValueError('uniform RefSet needs per_video dividing the row count')
             self.offsets = None
             self.max_refs = int(per_video)
@@ -54,9 +54,27 @@ class RefSet:
             self.max_refs = int(np.diff(off).max()) if len(off) > 1 else 0
             self.n_videos = len(off) - 1
 
+    def __len__(self):
+        return self.n_videos
+
+    def __getitem__(self, videos):
+        """A contiguous slice of the videos (what ``dist.shard_batch`` takes of ``data_gts``)."""
+        if not isinstance(videos, slice):
+            raise TypeError('RefSet supports slices of videos')
+        lo, hi, step = videos.indices(self.n_videos)
+        if step != 1:
+            raise ValueError('RefSet slices must be contiguous')
+        hi = max(hi, lo)
+        if self.offsets is None:
+            return RefSet(self.rows[lo * self.max_refs:hi * self.max_refs], per_video=self.max_refs)
+        off = self.offsets[lo:hi + 1].cpu().numpy()
+        return RefSet(self.rows[int(off[0]):int(off[-1])], offsets=off - off[0])
+
     @classmethod
     def from_list(cls, data_gts, device):
         counts = [len(g) for g in data_gts]
+        if not counts:                                   # an empty shard: no videos, no rows
+            return cls(torch.zeros((0, 1), dtype=torch.int32, device=device), offsets=np.zeros(1, dtype=np.int64))
         rows = np.concatenate([np.asarray(g).reshape(len(g), -1) for g in data_gts], axis=0)
         if rows.dtype.kind not in 'iu':
             if np.any(rows != np.floor(rows)):
@@ -234,6 +252,8 @@ def _launch_reward(scorer, sampled, greedy, refs, cands_per_video, use_eos, mode
     reward = torch.empty(n, dtype=torch.float32, device=dev)
     stats = (torch.zeros if n == 0 else torch.empty)(_lib.N_STATS, dtype=torch.float64, device=dev)
     fused = cands_per_video == seq_per_img
+    if n == 0:                                           # an empty shard: zero statistics, nothing to launch
+        return reward, stats, (torch.empty(0, dtype=torch.float64, device=dev) if want_scores or not fused else None)
     scores = None
     if want_scores or not fused:
         scores = torch.empty(n * (2 if greedy is not None else 1), dtype=torch.float64, device=dev)

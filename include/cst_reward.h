@@ -220,7 +220,13 @@ int cst_reward(const cst_df_table* table,
  *   - All calls on a device share the one array: two calls whose kernels overlap on
  *     the GPU (different streams) race on it.  Serialise them.
  *   - It calls no cudaMalloc / cudaFree or other allocating routine; its counters are
- *     cleared on the caller's stream at the start of every call. */
+ *     cleared on the caller's stream at the start of every call.
+ *   - One thing still allocates, and not in this library: under CUDA's default lazy module
+ *     loading the DRIVER loads a kernel's code at its first launch, which takes device memory.
+ *     The entry point launches the scoring kernel, the statistics fold (batches of 2,368 videos
+ *     or more on a B200) and, when cands_per_video != seq_per_img, the baseline kernel: make one
+ *     small call of each shape you will use BEFORE the pool takes the memory, or run with
+ *     CUDA_MODULE_LOADING=EAGER. */
 #define CST_NOALLOC_MAX_GROUPS 16384
 int cst_reward_noalloc(const cst_df_table* table,
                        const void* cand, const void* greedy, int32_t cand_dtype,
@@ -240,16 +246,18 @@ int cst_reward_noalloc(const cst_df_table* table,
  * although the ground-truth captions never change during training.  cst_refs_cook runs that
  * half of the scoring kernel ONCE per video and keeps the result in device memory -- the
  * per-video n-gram table with its presence masks, the refs' inverse norms and lengths: one
- * image of cst_refs_cooked_bytes() per video, about 46 KB for 20 refs of width 30 (MSR-VTT's
- * 10 k videos: 0.47 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
+ * image of cst_refs_cooked_bytes() = 26,624 bytes per video whatever the row width and count
+ * (MSR-VTT's 10 k videos: 0.27 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
  * images of the videos named by image_index (device int64, one per video of the batch; NULL =
  * images 0..n_videos-1 in order): a step passes video indices instead of reference rows.
  * The indices are not range-checked (that would need a host read): every one must name an
  * image inside the buffer.
  * Images depend on the df table, use_eos, ref_width and refs_per_video they were cooked with;
  * an image of another layout, table geometry or use_eos makes the rewards of that video NaN
- * and is counted in stats_out[4].  At most 32 refs per video (a video with more gets an
- * invalid image).  bad_rows_out (device, optional, caller zeroes it): += reference rows that
+ * and is counted in stats_out[4].  An image is ONE table: at most 32 refs per video and at most
+ * 1,400 n-gram instances over them (sum over the refs of 4 L - 6 for L tokens: 20 refs of up to 19
+ * tokens on average); a video beyond that gets an invalid image -- score it from raw rows, where
+ * the kernel works through the references in chunks.  bad_rows_out (device, optional, caller zeroes it): += reference rows that
  * held ids outside [-1, 65534], += 1 per invalid image. */
 int64_t cst_refs_cooked_bytes(int32_t ref_width, int32_t refs_per_video);   /* -1: out of range */
 int cst_refs_cook(const cst_df_table* table,
@@ -270,6 +278,26 @@ int cst_reward_cooked(const cst_df_table* table,
                       const double* bcmrscores,
                       float* reward_out, double* scores_out, double* stats_out,
                       void* scratch, int64_t scratch_bytes, void* stream);
+
+/* ---- leave-one-out document frequencies (GT consensus scores) ----------------------------
+ * compute_scores.py:75-103 (make compute_evalscores, --remove_in_ref) scores caption i of every video
+ * against the video's other captions with coco-caption's Cider in corpus mode: the document
+ * frequency is recomputed from the references of that call, i.e. from all captions but the i-th
+ * of every video -- twenty rebuilds of the table in the reference.  They differ from the df of ALL
+ * captions only where caption i is a video's sole holder of an n-gram:
+ *     df_i(g) = df_all(g) - #{videos whose caption i alone holds g}.
+ * cst_df_sole_holders counts those per (caption, table slot) in one pass over the rows the table was
+ * built from (cst_df_build_from_rows; `per_video` <= 32 captions per video, uniform):
+ *     excl_out [dev] uint32 [per_video][cst_df_capacity(table)], zeroed by the caller;
+ *     too_large_out [dev] uint32, optional, zeroed by the caller: += 1 per video whose captions hold
+ *     more than 1,400 n-gram instances (not counted: fall back to one table per pass).
+ * cst_df_leave_one_out then switches the table's idf to pass `caption` (idf = log N - log max(1,
+ * df_all - excl[caption])) in one streaming kernel; scoring calls on the same stream afterwards see
+ * that pass.  The table stays in that state: it belongs to the consensus computation. */
+int cst_df_sole_holders(const cst_df_table* table, const void* rows, int32_t dtype, int64_t n_rows,
+                        int32_t width, int64_t stride, int32_t per_video, int64_t n_videos,
+                        int32_t use_eos, uint32_t* excl_out, uint32_t* too_large_out, void* stream);
+int cst_df_leave_one_out(cst_df_table* table, const uint32_t* excl, int32_t caption, void* stream);
 
 /* Baseline alone on given scores: utils.py:286-288 (WXE: scores are the
  * precomputed consensus scores) and utils.py:292-322.  scores [dev] float64
