@@ -700,7 +700,7 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
         rc = launch_mode<CST2_MODE_RAW>(p, grid, smem, dev, st);
     if (rc != CST_OK) return rc;
     if (p.fold_apart) {
-        k_fold_stats<<<1, 256, 2 * 8 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);
+        k_fold_stats<<<1, 1024, 2 * 32 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);
         COUNT_LAUNCH();
         CUDA_TRY(cudaGetLastError());
     }
