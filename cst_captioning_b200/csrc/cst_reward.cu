@@ -656,18 +656,18 @@ static int device_sms(int dev, int* sms) {
     return CST_OK;
 }
 
-template <int MODE>
+template <int MODE, int ESZ>
 static int launch_mode(const ScoreParams& p, unsigned grid, size_t smem, int dev, cudaStream_t st) {
     {
         static size_t set[64] = {0};                  // (one array per instantiation)
         std::lock_guard<std::mutex> lock(g_smem_mutex);
         if (dev < 0 || dev >= 64 || set[dev] < smem) {
-            CUDA_TRY(cudaFuncSetAttribute(k_score2<MODE, CST2_WARPS, CST2_CTAS>,
+            CUDA_TRY(cudaFuncSetAttribute(k_score2<MODE, CST2_WARPS, CST2_CTAS, ESZ>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             if (dev >= 0 && dev < 64) set[dev] = smem;
         }
     }
-    k_score2<MODE, CST2_WARPS, CST2_CTAS><<<grid, CST2_WARPS * 32, smem, st>>>(p);
+    k_score2<MODE, CST2_WARPS, CST2_CTAS, ESZ><<<grid, CST2_WARPS * 32, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
@@ -690,14 +690,19 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
     p.fold_apart = (p.mode >= 0 && !p.cook_out && !p.excl && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
     p.prefetch_ahead = sms * CST2_CTAS;
+    // int32 rows on both sides (what the device-resident training loop passes) take an instantiation with
+    // the element size compiled in; int16 / int64 / mixed rows the run-time one
+    const bool i32 = p.cand_esz == 4 && (p.cooked || p.ref_esz == 4);
     if (p.excl)
-        rc = launch_mode<CST2_MODE_EXCL>(p, grid, smem, dev, st);
+        rc = launch_mode<CST2_MODE_EXCL, 0>(p, grid, smem, dev, st);
     else if (p.cook_out)
-        rc = launch_mode<CST2_MODE_COOK>(p, grid, smem, dev, st);
+        rc = launch_mode<CST2_MODE_COOK, 0>(p, grid, smem, dev, st);
     else if (p.cooked)
-        rc = launch_mode<CST2_MODE_STAGED>(p, grid, smem, dev, st);
+        rc = i32 ? launch_mode<CST2_MODE_STAGED, 4>(p, grid, smem, dev, st)
+                 : launch_mode<CST2_MODE_STAGED, 0>(p, grid, smem, dev, st);
     else
-        rc = launch_mode<CST2_MODE_RAW>(p, grid, smem, dev, st);
+        rc = i32 ? launch_mode<CST2_MODE_RAW, 4>(p, grid, smem, dev, st)
+                 : launch_mode<CST2_MODE_RAW, 0>(p, grid, smem, dev, st);
     if (rc != CST_OK) return rc;
     if (p.fold_apart) {
         k_fold_stats<<<1, 1024, 2 * 32 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);

@@ -33,12 +33,14 @@
 #define CST2_ROWS 32                 /* rows per batch: presence bits of a chunk, lanes of the prefix scan */
 #define CST2_TOK_STRIDE 32
 #ifndef CST2_LIST_CAP
-#define CST2_LIST_CAP 960            /* n-gram instances per batch (16 B each) */
+#define CST2_LIST_CAP 832            /* n-gram instances per batch (16 B each) */
 #endif
 #ifndef CST2_TAB_SLOTS
-#define CST2_TAB_SLOTS 1531          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
+#define CST2_TAB_SLOTS 1201          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
 #endif
-#define CST2_TAB_BUDGET 1400         /* n-gram instances a table takes before a new chunk starts */
+#ifndef CST2_TAB_BUDGET
+#define CST2_TAB_BUDGET 1100         /* n-gram instances a table takes before a new chunk starts */
+#endif
 #define CST2_MODE_RAW 0
 #define CST2_MODE_STAGED 1
 #define CST2_MODE_COOK 2
@@ -48,13 +50,12 @@
 #define CST2_WARPS 8
 #endif
 #ifndef CST2_CTAS
-#define CST2_CTAS 5
+#define CST2_CTAS 6
 #endif
 
 #ifndef CST2_PREFETCH
 #define CST2_PREFETCH 1     /* L2 prefetch of the rows a later CTA will start on (measured: 2 % of the step) */
 #endif
-
 typedef unsigned short u16;
 
 struct __align__(16) RefA {          // what a presence bit needs of its reference, one 16-byte load
@@ -334,6 +335,10 @@ __device__ __forceinline__ void v2_process(const ScoreParams& p, bool is_r, uint
     }
 }
 
+__device__ __forceinline__ void v2_prefetch_l2(const void* p, u32 bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 // shared-memory layout: everything the hot loops touch sits at a compile-time offset.  The first
 // three pieces -- header, reference norms / lengths, table -- are what the reference stages of a
 // video leave behind: contiguous, so that a staged-reference image is one copy in either direction.
@@ -367,7 +372,8 @@ static_assert(CST2_IMG_BYTES % 16 == 0 && CST2_OFF_TAB % 16 == 0, "the image mus
 // copy of the code:   load + canonicalise | scan + emit | process   with a CTA barrier after each;
 // a reference stage ends with the norms of its rows, a candidate stage with the sums of its
 // segments.  A video of the training shapes is one stage of each kind.
-template <int MODE, int NW, int CTAS>
+// ESZ: bytes per token id when the launch fixes them for both row sets (4: int32 rows), 0: run-time
+template <int MODE, int NW, int CTAS, int ESZ>
 __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     constexpr int NT = NW * 32;
     constexpr u32 T = CST2_TAB_SLOTS;
@@ -382,6 +388,8 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
     const int n_local = S * (p.greedy ? 2 : 1);
+    // candidate rows per batch: even shares (40 rows go as 20 + 20, not 32 + 8)
+    const int cand_rows = (n_local + (n_local + CST2_ROWS - 1) / CST2_ROWS - 1) / ((n_local + CST2_ROWS - 1) / CST2_ROWS > 0 ? (n_local + CST2_ROWS - 1) / CST2_ROWS : 1);
 
     u32* hdr = reinterpret_cast<u32*>(smem);                                  // [4]
     RefA* refA = reinterpret_cast<RefA*>(smem + CST2_OFF_REFA);               // [4][32]
@@ -433,14 +441,12 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
                 if (!STAGED) {
                     const char* a = reinterpret_cast<const char*>(p.refs) + (size_t)(v2 * p.refs_per_video) * pitch_r;
                     const u32 na = ((u32)p.refs_per_video * pitch_r) & ~15u;
-                    if (na && !(reinterpret_cast<uintptr_t>(a) & 15u))
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"(na) : "memory");
+                    if (na && !(reinterpret_cast<uintptr_t>(a) & 15u)) v2_prefetch_l2(a, na);
                 }
                 if (!COOK) {
                     const char* b = reinterpret_cast<const char*>(p.cand) + (size_t)(v2 * S) * pitch_c;
                     const u32 nb = ((u32)S * pitch_c) & ~15u;
-                    if (nb && !(reinterpret_cast<uintptr_t>(b) & 15u))
-                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b), "r"(nb) : "memory");
+                    if (nb && !(reinterpret_cast<uintptr_t>(b) & 15u)) v2_prefetch_l2(b, nb);
                 }
             }
         }
@@ -467,9 +473,9 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
             // issued before any is used ----
             const int room = CST2_ROWS - chunk_rows;
             const int n_try = is_r ? (int)((r1 - rbase) < room ? (r1 - rbase) : room)
-                                   : ((n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS);
+                                   : ((n_local - cb) < cand_rows ? (n_local - cb) : cand_rows);
             {
-                const int esz = is_r ? p.ref_esz : p.cand_esz;
+                const int esz = ESZ ? ESZ : (is_r ? p.ref_esz : p.cand_esz);
                 const u32 pitch = is_r ? pitch_r : pitch_c;
                 const char* base = is_r ? reinterpret_cast<const char*>(p.refs) + (size_t)rbase * pitch_r
                                         : reinterpret_cast<const char*>(p.cand) + (size_t)(video * S) * pitch_c;
