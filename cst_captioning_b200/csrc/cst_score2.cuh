@@ -36,7 +36,7 @@
 #define CST2_LIST_CAP 832            /* n-gram instances per batch (16 B each) */
 #endif
 #ifndef CST2_TAB_SLOTS
-#define CST2_TAB_SLOTS 1201          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
+#define CST2_TAB_SLOTS 1193          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
 #endif
 #ifndef CST2_TAB_BUDGET
 #define CST2_TAB_BUDGET 1100         /* n-gram instances a table takes before a new chunk starts */

@@ -29,7 +29,7 @@ ANCHORS = [
     ('process: presence bits -> table (references)', 'if (EXCL) {'),
     ('process: bit walk (candidates)', 'const int idx = v2_find<T, BOUNDED>(tab, h, key);'),
     ('process: slot store', 'double2* out = reinterpret_cast<double2*>(list + i);'),
-    ('prologue, per-video set-up, prefetch', 'template <int MODE, int NW, int CTAS>'),
+    ('prologue, per-video set-up, prefetch', 'template <int MODE, int NW, int CTAS, int ESZ>'),
     ('stage: row loads + canonicalise call', '// ---- load + canonicalise the stage'),
     ('stage: scan + emit loop', '// ---- scan + emit'),
     ('stage: process call + barriers', '// ---- process ----'),

@@ -25,8 +25,8 @@ t1 = scratch[64:64 + 128].clone().view(torch.int64).cpu().numpy()
 d = (t1 - t0).astype(np.float64)
 warps = 8 * n
 names = ['R load+canon', 'R barrier 1', 'R scan+emit', 'R barrier 2', 'R process', 'R barrier 3',
-         'C (load+canon)', 'C barrier 1', 'C scan+emit', 'C barrier 2', 'C process', 'C barrier 3',
-         'R norms', 'C sums (warp 0)', 'tail warp 0', 'tail other warps']
+         'C load+canon', 'C barrier 1', 'C scan+emit', 'C barrier 2', 'C process', 'C barrier 3',
+         'segment sums (both)', 'tail: scores, baseline', '-', '-']
 for nm, v in zip(names, d / warps):
     print('%-22s %10.0f cycles per warp per video' % (nm, v))
 print('total %10.0f' % (d.sum() / warps))
