@@ -14,7 +14,7 @@ g}``.  So the table is built ONCE from all rows, one more pass over the rows cou
 per (caption, n-gram) (``cst_df_sole_holders``), and pass i switches the table's idf to
 ``log V - log max(1, df_all - excl_i)`` with one streaming kernel (``cst_df_leave_one_out``) before
 scoring column i against the rest with the same fused kernel as the RL path.  Videos whose captions
-exceed one shared-memory table (more than 32 captions or 1,400 n-gram instances) fall back to one
+exceed one shared-memory table (more than 32 captions or 1,100 n-gram instances) fall back to one
 device-built table per pass.
 
 Difference in input, not in arithmetic: the reference scores the raw caption *words*

@@ -246,8 +246,8 @@ int cst_reward_noalloc(const cst_df_table* table,
  * although the ground-truth captions never change during training.  cst_refs_cook runs that
  * half of the scoring kernel ONCE per video and keeps the result in device memory -- the
  * per-video n-gram table with its presence masks, the refs' inverse norms and lengths: one
- * image of cst_refs_cooked_bytes() = 26,624 bytes per video whatever the row width and count
- * (MSR-VTT's 10 k videos: 0.27 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
+ * image of cst_refs_cooked_bytes() = 21,248 bytes per video whatever the row width and count
+ * (MSR-VTT's 10 k videos: 0.21 GB of the 180 GB).  cst_reward_cooked then scores a batch against the
  * images of the videos named by image_index (device int64, one per video of the batch; NULL =
  * images 0..n_videos-1 in order): a step passes video indices instead of reference rows.
  * The indices are not range-checked (that would need a host read): every one must name an
@@ -255,7 +255,7 @@ int cst_reward_noalloc(const cst_df_table* table,
  * Images depend on the df table, use_eos, ref_width and refs_per_video they were cooked with;
  * an image of another layout, table geometry or use_eos makes the rewards of that video NaN
  * and is counted in stats_out[4].  An image is ONE table: at most 32 refs per video and at most
- * 1,400 n-gram instances over them (sum over the refs of 4 L - 6 for L tokens: 20 refs of up to 19
+ * 1,100 n-gram instances over them (sum over the refs of 4 L - 6 for L tokens: 20 refs of up to 15
  * tokens on average); a video beyond that gets an invalid image -- score it from raw rows, where
  * the kernel works through the references in chunks.  bad_rows_out (device, optional, caller zeroes it): += reference rows that
  * held ids outside [-1, 65534], += 1 per invalid image. */
@@ -290,7 +290,7 @@ int cst_reward_cooked(const cst_df_table* table,
  * built from (cst_df_build_from_rows; `per_video` <= 32 captions per video, uniform):
  *     excl_out [dev] uint32 [per_video][cst_df_capacity(table)], zeroed by the caller;
  *     too_large_out [dev] uint32, optional, zeroed by the caller: += 1 per video whose captions hold
- *     more than 1,400 n-gram instances (not counted: fall back to one table per pass).
+ *     more than 1,100 n-gram instances (not counted: fall back to one table per pass).
  * cst_df_leave_one_out then switches the table's idf to pass `caption` (idf = log N - log max(1,
  * df_all - excl[caption])) in one streaming kernel; scoring calls on the same stream afterwards see
  * that pass.  The table stays in that state: it belongs to the consensus computation. */
