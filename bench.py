@@ -456,6 +456,22 @@ def product_arm(args):
            'ms_per_step': 1e3 * e2e_s / args.steps,
            'same_bits_as_device_resident': bool(torch.equal(out_pin.to(dev), rew[:, 0]))}
 
+    # the platform's ceiling for that leg: the same pinned bytes uploaded by plain copies, every rank at
+    # once (N ranks share the host's PCIe fabric), no kernels of ours -- max over ranks like every timing
+    d_c, d_r = torch.empty_like(d_cand), torch.empty_like(h_refs, device=dev)
+    for _ in range(2):
+        d_c.copy_(h_cand, non_blocking=True)
+        d_r.copy_(h_refs, non_blocking=True)
+    plain_ms = max_over_ranks(event_ms(lambda: (d_c.copy_(h_cand, non_blocking=True), d_r.copy_(h_refs, non_blocking=True)),
+                                       10, barrier))
+    h2d_bytes = e2e['h2d_bytes_per_step']
+    e2e['plain_copy'] = {'ms_per_step': plain_ms, 'GBs_per_gpu': h2d_bytes / plain_ms / 1e6,
+                         'GBs_all_gpus': world * h2d_bytes / plain_ms / 1e6,
+                         'e2e_over_plain_copy': plain_ms / e2e['ms_per_step'],
+                         'note': 'upload of the step\'s pinned rows alone, all ranks concurrently: what the host '
+                                 'platform allows; the end-to-end step cannot be shorter'}
+    del d_c, d_r
+
     # informational: the same pipeline fed int16 host rows (ids <= 32767 fit; half the upload)
     h_cand16, h_refs16 = h_cand.to(torch.int16).pin_memory(), h_refs.to(torch.int16).pin_memory()
 
