@@ -581,6 +581,8 @@ struct ScoreParams {
     int prefetch_ahead;             // k_score2: how many videos ahead a CTA prefetches rows into L2
     u32* excl;                      // leave-one-out counts [caption][df slot] (CST2_MODE_EXCL)
     size_t excl_stride;             // = df slots
+    int n_local;                    // k_score2: candidate rows per video (cands_per_video, twice with greedy rows)
+    int cand_rows;                  // k_score2: candidate rows per batch
 };
 
 #ifndef CST_FOLD_APART_CTAS
@@ -680,6 +682,9 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     p.tab_slots = CST2_TAB_SLOTS;
     p.list_cap = CST2_LIST_CAP;
     const int n_local = p.cands_per_video * (p.greedy ? 2 : 1);
+    const int n_batches = (n_local + CST2_ROWS - 1) / CST2_ROWS;
+    p.n_local = n_local;
+    p.cand_rows = n_batches ? (n_local + n_batches - 1) / n_batches : 1;
     const size_t smem = score2_smem(n_local, p.cands_per_video, CST2_WARPS);
     if (smem > 227 * 1024) return fail(CST_E_RANGE, "scoring needs %zu bytes of shared memory per CTA", smem);
     int dev = 0;

@@ -1,33 +1,35 @@
-// k_score2 -- the raw-row scoring kernel of round 2 (included by cst_reward.cu after ScoreParams).
+// k_score2 -- the scoring kernel (included by cst_reward.cu after ScoreParams).
 //
-// Same arithmetic as k_score (CIDEr-D of every candidate against its video's references, then the
-// baseline of utils.py:292-322), reorganised around ONE idea: the expensive per-n-gram work -- the df
-// probe into the L2-resident table, the insert / find in the per-video shared-memory table, the walk
-// over the presence bits -- runs over a dense LIST of n-gram instances with every lane busy, instead
-// of "lane = token position, four orders per lane" where a third of the lanes idle and the four
-// order bodies diverge.  One CTA per video:
+// CIDEr-D of every candidate against its video's references, then the baseline of utils.py:292-322.
+// The kernel is organised around ONE idea: the expensive per-n-gram work -- the df probe into the
+// L2-resident table, the insert / find in the per-video shared-memory table, the walk over the
+// presence bits -- runs over a dense LIST of n-gram instances with every lane busy (round 1's kernel
+// put a token position on a lane and unrolled the four orders per lane: a third of the lanes idled
+// and the order bodies diverged).  One CTA of 8 warps per video, 6 CTAs per SM:
 //
 //   canon    warp per row, lane = raw position: ballot/popc compaction of utils.py:135-152
 //            (array_to_str) -> canonical token codes (u16) + length per row in shared memory
 //   emit     half-warp per row (full warp for rows longer than 16 tokens), lane = start position:
 //            packed 1..4-gram keys, term frequency and "first occurrence" from one MATCH.ANY
-//            (compute_ciderdf.py:19-34, precook); instance (row, order k, position) owns list slot
-//            off[row] + koff(k) + position -- a layout known from the row lengths alone, so no
-//            compaction pass and no atomics; repeats inside a row leave their slot empty
+//            (compute_ciderdf.py:19-34, precook); instance (order k, row, position) owns a list slot
+//            known from the row lengths alone (order-major, see V2Scan), so no compaction pass and
+//            no atomics; repeats inside a row leave their slot marked empty
 //   process  thread per list slot: idf (direct load for unigrams, one 32-byte bucket otherwise);
 //            references: insert into the video table, OR the row's presence bit; candidates: find,
 //            walk the presence bits.  The slot is overwritten with {(tf idf)^2, idf^2 * inner}
 //   sums     thread per (row, order): its list segment is contiguous, summed front to back ->
 //            norms, numerators.  No floating-point atomics, no shuffle trees: deterministic.
 //
-// Shared memory is a fixed 44 KB whatever the row widths and counts.  References enter the video
-// table in sub-stages of at most CST2_LIST_CAP instances; a video with more than 32 references or
-// more than CST2_TAB_BUDGET instances is scored in several chunks, each with a table of its own
+// Shared memory is a fixed 37 KB whatever the row widths and counts.  References enter the video
+// table in stages of at most CST2_LIST_CAP instances; a video with more than 32 references or more
+// than CST2_TAB_BUDGET instances is scored in several chunks, each with a table of its own
 // (CIDEr-D adds over references); candidates go through in batches likewise.
 //
-// Three instantiations of the one source (MODE): raw rows; COOK -- the reference half only, its
-// result (header, norms and lengths, table) written out as the video's image; STAGED -- that half
-// replaced by one bulk asynchronous copy of the image (cst_refs_cook / cst_reward_cooked).
+// Instantiations of the one source (MODE): raw rows; COOK -- the reference stages only, their
+// result (header, norms and lengths, table) written out as the video's image; STAGED -- those
+// stages replaced by one bulk asynchronous copy of the image (cst_refs_cook / cst_reward_cooked);
+// EXCL -- the reference stages counting leave-one-out document frequencies (cst_df_sole_holders).
+// The sizes below were settled by measurement (profiles/README.md, round 2).
 #pragma once
 
 #define CST2_ROWS 32                 /* rows per batch: presence bits of a chunk, lanes of the prefix scan */
@@ -36,7 +38,7 @@
 #define CST2_LIST_CAP 832            /* n-gram instances per batch (16 B each) */
 #endif
 #ifndef CST2_TAB_SLOTS
-#define CST2_TAB_SLOTS 1193          /* per-video table; a chunk inserts at most CST2_LIST_CAP keys */
+#define CST2_TAB_SLOTS 1193          /* per-video table (prime: double hashing); a chunk inserts <= CST2_TAB_BUDGET keys */
 #endif
 #ifndef CST2_TAB_BUDGET
 #define CST2_TAB_BUDGET 1100         /* n-gram instances a table takes before a new chunk starts */
@@ -387,9 +389,9 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
     // (through a shuffle so that the compiler knows the value is the same in all lanes of the warp)
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
-    const int n_local = S * (p.greedy ? 2 : 1);
-    // candidate rows per batch: even shares (40 rows go as 20 + 20, not 32 + 8)
-    const int cand_rows = (n_local + (n_local + CST2_ROWS - 1) / CST2_ROWS - 1) / ((n_local + CST2_ROWS - 1) / CST2_ROWS > 0 ? (n_local + CST2_ROWS - 1) / CST2_ROWS : 1);
+    // (both computed by the host: the compiler would rather recompute than keep them)
+    const int n_local = p.n_local;                      // candidate rows per video: S, or 2 S with greedy rows
+    const int cand_rows = p.cand_rows;                  // per batch, in even shares (40 rows go as 20 + 20, not 32 + 8)
 
     u32* hdr = reinterpret_cast<u32*>(smem);                                  // [4]
     RefA* refA = reinterpret_cast<RefA*>(smem + CST2_OFF_REFA);               // [4][32]
