@@ -61,8 +61,8 @@ __host__ __device__ __forceinline__ u32 cst_slot(u32 h, u32 cap) {
 #ifdef __CUDACC__
 
 // One bucket = 4 keys = 32 bytes = one sector, fetched by a single LDG.256.  Not allocated in L1:
-// probes land all over a 36 MB array, and the 28 KB of L1 an SM has left next to four per-video
-// tables are better spent on the token rows and the unigram idf (3.22 -> 3.11 ms).
+// probes land all over a 36 MB array, and the little L1 an SM has left next to the per-video
+// tables is better spent on the token rows and the unigram idf (round 1: 3.22 -> 3.11 ms).
 __device__ __forceinline__ void ld_bucket(const u64* p, u64 k[4]) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u64 {%0,%1,%2,%3}, [%4];"
                  : "=l"(k[0]), "=l"(k[1]), "=l"(k[2]), "=l"(k[3])
@@ -72,8 +72,7 @@ __device__ __forceinline__ void ld_bucket(const u64* p, u64 k[4]) {
 // slot index of `key` (>= 0), or -1 if absent.  `b` is the home bucket, `k` its
 // already loaded keys.  Overflow into the next bucket is rare (load factor 0.5).
 // MARK: also stop at a full bucket whose first two keys are in ascending order (see the layout
-// note above).  The raw-row scoring kernel is compiled without it: there the extra test tipped
-// the register allocation (3.40 -> 3.46 ms), while every other caller gains from the shorter walks.
+// note above).  (The scoring kernel has its own compact form of this walk, v2_resolve.)
 template <bool MARK = true>
 __device__ __forceinline__ int bucket_resolve(const u64* __restrict__ keys, u32 nb, u32 b, u64 k[4], u64 key) {
     for (;;) {
@@ -87,42 +86,13 @@ __device__ __forceinline__ int bucket_resolve(const u64* __restrict__ keys, u32 
     }
 }
 
-// idf of the four n-grams of a lane.  Order 1 is a direct load; the bucket loads of
-// orders 2..4 are issued back to back so their L2 round trips overlap, then the
-// idf loads of the slots that matched.
-template <bool MARK = true>
-__device__ __forceinline__ void df_probe4(const DfView& t, const u64 key[4], const u32 h[4], const bool need[4],
-                                          double idf[4]) {
-    const u32 tok = (u32)key[0] - 1u;
-    double w0 = t.unseen;
-    if (need[0] && tok < CST_UNI_N) w0 = __ldg(t.uni + tok);
-    u32 b[4];
-    u64 kk[4][4];
-#pragma unroll
-    for (int k = 1; k < 4; ++k) {
-        b[k] = need[k] ? cst_slot(h[k], t.n_buckets) : 0u;
-        ld_bucket(t.keys + (size_t)b[k] * CST_BUCKET, kk[k]);
-    }
-    int slot[4];
-#pragma unroll
-    for (int k = 1; k < 4; ++k)
-        slot[k] = need[k] ? bucket_resolve<MARK>(t.keys, t.n_buckets, b[k], kk[k], key[k]) : -1;
-    idf[0] = w0;
-#pragma unroll
-    for (int k = 1; k < 4; ++k) idf[k] = (slot[k] >= 0) ? __ldg(t.idfv + slot[k]) : t.unseen;
-}
-
 __device__ __forceinline__ u32 lanemask_lt(int lane) { return (1u << lane) - 1u; }
 
 // ---------------------------------------------------------------------------
-// Row canonicalisation + n-gram keys.  A row is handled by a group of G lanes:
-// G = 32 (one row per warp) or G = 16 (two rows per warp, one per half -- captions
-// average 11 tokens, so half-warps double the useful lanes; rows whose canonical
-// length exceeds 16 yield no keys with G = 16 and are redone with G = 32 by the
-// caller).  G and the token width are RUN-TIME values on purpose: one copy of this
-// code serves references, candidates, both group sizes and both token types, which
-// keeps the scoring kernel small enough for the instruction cache (the first versions,
-// specialised four ways, were instruction-fetch bound).
+// Row canonicalisation + n-gram keys for the df build and the n-gram parity probe (the scoring
+// kernel has its own, leaner forms: v2_canon / v2_emit).  A row is handled by a group of G lanes:
+// G = 32 (one row per warp) or G = 16 (two rows per warp, one per half); G and the token width are
+// run-time values.
 // Restates utils.py:135-152 (array_to_str) and compute_ciderdf.py:28-33
 // (precook's k/i loops) on packed keys.
 //   key[k]   packed (k+1)-gram starting at the lane's position, 0 if none
@@ -150,25 +120,6 @@ __device__ __forceinline__ long long ld_tok(const void* row, int esz, int i) {
     if (esz == 4) return (long long)__ldcs(reinterpret_cast<const int*>(row) + i);
     if (esz == 8) return (long long)__ldcs(reinterpret_cast<const long long*>(row) + i);
     return (long long)__ldcs(reinterpret_cast<const short*>(row) + i);
-}
-
-// Canonical token count of a row only (the pre-scan that finds the rows too long for a
-// 16-lane group); same rules as canon_row.
-__device__ __forceinline__ int canon_len(const void* row, int esz, int width, int use_eos, int lane, int G) {
-    const int sl = grp_sl(lane, G);
-    const bool half = (G == 16);
-    const int pa = sl, pb = sl + 16;
-    const bool ina = pa < width;
-    const bool inb = half && pb < width;
-    const long long ta = ina ? ld_tok(row, esz, pa) : 0ll;
-    const long long tb = inb ? ld_tok(row, esz, pb) : 0ll;
-    const bool bada = ina && (ta < -1 || ta > 65534);
-    const bool badb = inb && (tb < -1 || tb > 65534);
-    const u32 tmask = grp_vote(ina && (ta == 0 || ta == -1 || bada), inb && (tb == 0 || tb == -1 || badb), lane, G);
-    const int end = tmask ? (__ffs(tmask) - 1) : width;
-    const bool keepa = (pa < end && ta != 1) || (use_eos && pa == end && ina && ta == 0);
-    const bool keepb = half && ((pb < end && tb != 1) || (use_eos && pb == end && inb && tb == 0));
-    return __popc(grp_vote(keepa, keepb, lane, G));
 }
 
 __device__ __forceinline__ bool canon_row(const void* row, int esz, int width, int use_eos, int lane, int G,
@@ -244,38 +195,6 @@ __device__ __forceinline__ void row_tf(const u64 key[4], int lane, int G, int on
     }
 }
 
-// Sum four per-lane doubles over a lane group with a transposed butterfly (G = 32:
-// 6 exchanges instead of 20).  On return every lane holds the group total of ONE of
-// the four inputs: order o = group_order(lane, G).
-__device__ __forceinline__ double group_sum4_transposed(const double v[4], int lane, int G) {
-    const int HI = G >> 1, MID = G >> 2;
-    const bool hi = (lane & HI) != 0;
-    const bool mid = (lane & MID) != 0;
-    // exchange with lane^HI: low half keeps orders {0,1}, high half keeps {2,3}
-    const double sendA = hi ? v[0] : v[2];
-    const double sendB = hi ? v[1] : v[3];
-    double keepA = hi ? v[2] : v[0];
-    double keepB = hi ? v[3] : v[1];
-    keepA += __shfl_xor_sync(CST_FULL, sendA, HI);
-    keepB += __shfl_xor_sync(CST_FULL, sendB, HI);
-    // exchange with lane^MID: bit clear keeps the first of the pair, bit set the second
-    const double send = mid ? keepA : keepB;
-    double x = mid ? keepB : keepA;
-    x += __shfl_xor_sync(CST_FULL, send, MID);
-#pragma unroll 1
-    for (int o = MID >> 1; o > 0; o >>= 1) x += __shfl_xor_sync(CST_FULL, x, o);
-    return x;
-}
-__device__ __forceinline__ int group_order(int lane, int G) {
-    return ((lane & (G >> 1)) ? 2 : 0) + ((lane & (G >> 2)) ? 1 : 0);
-}
-// sum of the four per-order values held in group_sum4_transposed's layout
-__device__ __forceinline__ double group_sum_orders(double t, int G) {
-    t += __shfl_xor_sync(CST_FULL, t, G >> 1);
-    t += __shfl_xor_sync(CST_FULL, t, G >> 2);
-    return t;
-}
-
 __device__ __forceinline__ double inv_norm_of(double sumsq) {
     return sumsq > 0.0 ? rsqrt(sumsq) : 0.0;
 }
@@ -301,26 +220,5 @@ __device__ __forceinline__ u64 count_key(u32 slot, u32 r) {
 // The table capacity is any number (sized to the worst case of the staged refs, not
 // rounded to a power of two: shared memory decides how many CTAs fit an SM).
 __device__ __forceinline__ u32 vid_home(u32 h, u32 slots) { return __umulhi(h, slots); }
-
-__device__ __forceinline__ u32 vid_insert(VidSlot* tab, u32 slots, u32 idx, u64 key) {
-    for (;;) {
-        u64 cur = *reinterpret_cast<volatile u64*>(&tab[idx].key);
-        if (cur == key) return idx;
-        if (cur == 0ull) {
-            u64 old = atomicCAS(reinterpret_cast<u64*>(&tab[idx].key), 0ull, key);
-            if (old == 0ull || old == key) return idx;
-        }
-        idx = (idx + 1 == slots) ? 0u : idx + 1;
-    }
-}
-
-__device__ __forceinline__ int vid_find(const VidSlot* tab, u32 slots, u32 idx, u64 key) {
-    for (;;) {
-        u64 cur = tab[idx].key;
-        if (cur == key) return (int)idx;
-        if (cur == 0ull) return -1;
-        idx = (idx + 1 == slots) ? 0u : idx + 1;
-    }
-}
 
 #endif  // __CUDACC__

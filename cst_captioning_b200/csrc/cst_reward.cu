@@ -1,14 +1,8 @@
 // CIDEr-D reward path for B200 (sm_100a): kernels + C ABI (include/cst_reward.h).
 //
-// One CTA per video.  Phase R: one warp per reference caption canonicalises its
-// row, packs the 1..4-gram keys, fetches their idf from the L2-resident df table
-// and publishes "which refs contain this n-gram" into a shared-memory hash table
-// (the video's reference n-gram vectors, staged once and reused by every
-// candidate of the video).  Phase C: one warp per candidate does the same for its
-// row, walks the presence bits of the n-grams it shares with the refs and reduces
-// the clipped tf-idf cosine x Gaussian length penalty with warp shuffles.  Phase B:
-// the SCB / greedy baseline of utils.py:292-322 on the CTA's scores, reward write,
-// per-video statistics; the last CTA folds the statistics deterministically.
+// This file holds the df table (host build, device build, probes), the baseline-only kernel, the
+// fold of the per-video statistics and the host side of every entry point; the scoring kernel
+// itself (raw rows, staged references, cooking, leave-one-out counts) is csrc/cst_score2.cuh.
 //
 // No tensor cores: the work is sparse hashing, not a dense contraction.
 #include <math.h>
