@@ -151,7 +151,9 @@ class CookedRefs:
         self.bad_rows = bad_rows            # device uint32[1]: out-of-range ref rows + invalid images
 
     @classmethod
-    def cook(cls, data_gts, scorer, use_eos=0):
+    def cook(cls, data_gts, scorer, use_eos=0, check=True):
+        """``check``: read the count of videos that could not be staged back (one host sync, cooking is
+        a one-off) and warn about them -- their rewards would be NaN."""
         table = scorer.table
         dev = table.device
         refs = RefSet.coerce(data_gts, dev)
@@ -168,6 +170,13 @@ class CookedRefs:
                                 refs.rows.stride(0), refs.offsets.data_ptr() if refs.offsets is not None else None,
                                 max_refs, refs.n_videos, int(use_eos), images.data_ptr(), stride, bad.data_ptr(),
                                 _stream(dev)))
+        if check:
+            n_bad = int(bad.item())
+            if n_bad:
+                import warnings
+                warnings.warn('%d reference rows with ids outside [0, 65534] or videos beyond one staged image '
+                              '(32 refs, 1,100 n-gram instances): rewards of such videos come out NaN from staged '
+                              'references -- score them from raw rows' % n_bad, RuntimeWarning, stacklevel=2)
         return cls(images, stride, w, max_refs, use_eos, table, bad_rows=bad)
 
     def batch(self, video_ids):
