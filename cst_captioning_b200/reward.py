@@ -70,6 +70,19 @@ class RefSet:
         off = self.offsets[lo:hi + 1].cpu().numpy()
         return RefSet(self.rows[int(off[0]):int(off[-1])], offsets=off - off[0])
 
+    def take(self, video_ids):
+        """The rows of the named videos, in order, gathered on the device -> RefSet."""
+        ids = np.ascontiguousarray(video_ids, dtype=np.int64)
+        if self.offsets is None:
+            r = self.max_refs
+            rows = (ids[:, None] * r + np.arange(r)[None, :]).reshape(-1)
+            return RefSet(self.rows.index_select(0, torch.from_numpy(rows).to(self.rows.device)), per_video=r)
+        off = self.offsets.cpu().numpy()
+        counts = off[ids + 1] - off[ids]
+        new_off = np.concatenate([[0], np.cumsum(counts)])
+        rows = np.repeat(off[ids] - new_off[:-1], counts) + np.arange(new_off[-1])
+        return RefSet(self.rows.index_select(0, torch.from_numpy(rows).to(self.rows.device)), offsets=new_off)
+
     @classmethod
     def from_list(cls, data_gts, device):
         counts = [len(g) for g in data_gts]
@@ -138,22 +151,27 @@ class CookedRefs:
     ``CookedRefs.cook(refs, scorer, use_eos)`` builds the images from a :class:`RefSet` /
     ``(V, R, W)`` tensor / list of arrays; ``cooked.batch(video_ids)`` selects a step's videos
     (only the indices move); the result is accepted wherever ``data_gts`` is.  Images are
-    tied to the scorer's df table and to ``use_eos``; at most 32 refs per video.
+    tied to the scorer's df table and to ``use_eos``.  An image is ONE table: at most 32 refs and
+    1,100 n-gram instances per video.  Videos beyond that cannot be staged; ``cook`` finds them
+    (``invalid``), and ``batch(ids)`` with host-side ids hands back the raw rows of a batch that
+    names one of them, so the call scores it from raw rows instead of yielding NaN rewards.
     """
 
     def __init__(self, images, stride, ref_width, max_refs, use_eos, table, index=None, n_videos=None,
-                 bad_rows=None):
+                 bad_rows=None, source=None, invalid=None):
         self.images, self.stride = images, int(stride)
         self.ref_width, self.max_refs, self.use_eos = int(ref_width), int(max_refs), int(bool(use_eos))
         self.table = table
         self.index = index
         self.n_videos = int(n_videos if n_videos is not None else images.shape[0])
         self.bad_rows = bad_rows            # device uint32[1]: out-of-range ref rows + invalid images
+        self.source = source                # the raw rows, kept only when some video could not be staged
+        self.invalid = invalid              # host bool per staged video, or None when all are valid
 
     @classmethod
-    def cook(cls, data_gts, scorer, use_eos=0, check=True):
-        """``check``: read the count of videos that could not be staged back (one host sync, cooking is
-        a one-off) and warn about them -- their rewards would be NaN."""
+    def cook(cls, data_gts, scorer, use_eos=0, verify=True):
+        """``verify``: look the images over once they are written (one host sync; cooking is a one-off),
+        warn about videos that could not be staged and keep their raw rows for ``batch``."""
         table = scorer.table
         dev = table.device
         refs = RefSet.coerce(data_gts, dev)
@@ -170,14 +188,18 @@ class CookedRefs:
                                 refs.rows.stride(0), refs.offsets.data_ptr() if refs.offsets is not None else None,
                                 max_refs, refs.n_videos, int(use_eos), images.data_ptr(), stride, bad.data_ptr(),
                                 _stream(dev)))
-        if check:
-            n_bad = int(bad.item())
-            if n_bad:
-                import warnings
-                warnings.warn('%d reference rows with ids outside [0, 65534] or videos beyond one staged image '
-                              '(32 refs, 1,100 n-gram instances): rewards of such videos come out NaN from staged '
-                              'references -- score them from raw rows' % n_bad, RuntimeWarning, stacklevel=2)
-        return cls(images, stride, w, max_refs, use_eos, table, bad_rows=bad)
+        source = invalid = None
+        if verify and int(bad.item()):
+            import warnings
+            magic = images[:, :4].contiguous().view(torch.int32)[:, 0]
+            invalid = (magic != 0x43535432).cpu().numpy()                   # "CST2": a valid image's header
+            source = refs if invalid.any() else None
+            warnings.warn('%d videos beyond one staged image (32 refs, 1,100 n-gram instances) are scored from raw '
+                          'rows; %d reference rows hold ids outside [0, 65534]'
+                          % (int(invalid.sum()), int(bad.item()) - int(invalid.sum())), RuntimeWarning, stacklevel=2)
+            if not invalid.any():
+                invalid = None
+        return cls(images, stride, w, max_refs, use_eos, table, bad_rows=bad, source=source, invalid=invalid)
 
     def batch(self, video_ids):
         """The step's videos, in order: only the int64 indices go to the device."""
@@ -187,9 +209,12 @@ class CookedRefs:
             ids = np.ascontiguousarray(video_ids, dtype=np.int64)
             if ids.size and (ids.min() < 0 or ids.max() >= self.images.shape[0]):
                 raise ValueError('video index outside the %d staged videos' % self.images.shape[0])
+            if self.invalid is not None and ids.size and self.invalid[ids].any():
+                return self.source.take(ids)        # a video that could not be staged: this batch goes raw
             idx = torch.from_numpy(ids).to(self.images.device)
         return CookedRefs(self.images, self.stride, self.ref_width, self.max_refs, self.use_eos, self.table,
-                          index=idx, n_videos=idx.numel(), bad_rows=self.bad_rows)
+                          index=idx, n_videos=idx.numel(), bad_rows=self.bad_rows, source=self.source,
+                          invalid=self.invalid)
 
     def nbytes(self):
         return self.images.numel()
