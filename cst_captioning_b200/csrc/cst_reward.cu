@@ -652,21 +652,33 @@ static int device_sms(int dev, int* sms) {
     return CST_OK;
 }
 
-template <int MODE, int ESZ>
+template <int MODE, int ESZ, int NW, int CTAS>
 static int launch_mode(const ScoreParams& p, unsigned grid, size_t smem, int dev, cudaStream_t st) {
     {
         static size_t set[64] = {0};                  // (one array per instantiation)
         std::lock_guard<std::mutex> lock(g_smem_mutex);
         if (dev < 0 || dev >= 64 || set[dev] < smem) {
-            CUDA_TRY(cudaFuncSetAttribute(k_score2<MODE, CST2_WARPS, CST2_CTAS, ESZ>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            CUDA_TRY(cudaFuncSetAttribute(k_score2<MODE, NW, CTAS, ESZ>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)smem));
             if (dev >= 0 && dev < 64) set[dev] = smem;
         }
     }
-    k_score2<MODE, CST2_WARPS, CST2_CTAS, ESZ><<<grid, CST2_WARPS * 32, smem, st>>>(p);
+    k_score2<MODE, NW, CTAS, ESZ><<<grid, NW * 32, smem, st>>>(p);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
     return CST_OK;
+}
+
+// Batches that two CTAs per SM hold at once (BASELINE configs 1 and 3: 64 videos) are latency-bound: one
+// video's chain of stages is the whole call.  CTAs of 16 warps halve the rounds of every stage
+// (config 3 from a CUDA graph: 44.5 -> 34.3 us); at full occupancy the same CTAs would be 75 % slower.
+#define CST2_SMALL_WARPS 16
+#define CST2_SMALL_CTAS 2
+template <int MODE, int ESZ>
+static int launch_sized(const ScoreParams& p, unsigned grid, size_t smem_big, size_t smem_small, bool small, int dev,
+                        cudaStream_t st) {
+    return small ? launch_mode<MODE, ESZ, CST2_SMALL_WARPS, CST2_SMALL_CTAS>(p, grid, smem_small, dev, st)
+                 : launch_mode<MODE, ESZ, CST2_WARPS, CST2_CTAS>(p, grid, smem_big, dev, st);
 }
 
 // One launch of the scoring kernel (raw rows, from staged images, or cooking images), plus the fold of
@@ -680,7 +692,8 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     p.n_local = n_local;
     p.cand_rows = n_batches ? (n_local + n_batches - 1) / n_batches : 1;
     const size_t smem = score2_smem(n_local, p.cands_per_video, CST2_WARPS);
-    if (smem > 227 * 1024) return fail(CST_E_RANGE, "scoring needs %zu bytes of shared memory per CTA", smem);
+    const size_t smem_small = score2_smem(n_local, p.cands_per_video, CST2_SMALL_WARPS);
+    if (smem_small > 227 * 1024) return fail(CST_E_RANGE, "scoring needs %zu bytes of shared memory per CTA", smem_small);
     int dev = 0;
     CUDA_TRY(cudaGetDevice(&dev));
     int sms = 148;
@@ -690,21 +703,22 @@ static int launch_score2(const ScoreParams& p_in, cudaStream_t st) {
     // static stride (measured again this round: 1 / 2 / 4 / 8 / 16 CTAs per resident slot 2.25 / 2.23 /
     // 2.17 / 2.11 / 2.06 ms against 2.03)
     const unsigned grid = (unsigned)(p.n_videos < 0x7fffffffLL ? p.n_videos : 0x7fffffffLL);
+    const bool small = p.n_videos <= (int64_t)CST2_SMALL_CTAS * sms;
     p.fold_apart = (p.mode >= 0 && !p.cook_out && !p.excl && p.n_videos >= (int64_t)CST_FOLD_APART_CTAS * sms) ? 1 : 0;
     p.prefetch_ahead = sms * CST2_CTAS;
     // int32 rows on both sides (what the device-resident training loop passes) take an instantiation with
     // the element size compiled in; int16 / int64 / mixed rows the run-time one
     const bool i32 = p.cand_esz == 4 && (p.cooked || p.ref_esz == 4);
     if (p.excl)
-        rc = launch_mode<CST2_MODE_EXCL, 0>(p, grid, smem, dev, st);
+        rc = launch_mode<CST2_MODE_EXCL, 0, CST2_WARPS, CST2_CTAS>(p, grid, smem, dev, st);
     else if (p.cook_out)
-        rc = launch_mode<CST2_MODE_COOK, 0>(p, grid, smem, dev, st);
+        rc = launch_mode<CST2_MODE_COOK, 0, CST2_WARPS, CST2_CTAS>(p, grid, smem, dev, st);
     else if (p.cooked)
-        rc = i32 ? launch_mode<CST2_MODE_STAGED, 4>(p, grid, smem, dev, st)
-                 : launch_mode<CST2_MODE_STAGED, 0>(p, grid, smem, dev, st);
+        rc = i32 ? launch_sized<CST2_MODE_STAGED, 4>(p, grid, smem, smem_small, small, dev, st)
+                 : launch_sized<CST2_MODE_STAGED, 0>(p, grid, smem, smem_small, small, dev, st);
     else
-        rc = i32 ? launch_mode<CST2_MODE_RAW, 4>(p, grid, smem, dev, st)
-                 : launch_mode<CST2_MODE_RAW, 0>(p, grid, smem, dev, st);
+        rc = i32 ? launch_sized<CST2_MODE_RAW, 4>(p, grid, smem, smem_small, small, dev, st)
+                 : launch_sized<CST2_MODE_RAW, 0>(p, grid, smem, smem_small, small, dev, st);
     if (rc != CST_OK) return rc;
     if (p.fold_apart) {
         k_fold_stats<<<1, 1024, 2 * 32 * sizeof(double), st>>>(p.ctl, p.partials, p.n_videos, p.n_m, p.n_b, p.stats);
