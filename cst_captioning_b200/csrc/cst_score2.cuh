@@ -672,6 +672,9 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
         }
         if (STAGED && bad_image && threadIdx.x == 0) ++bad_rows;
         if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+        // (the GT-consensus score of this lane's caption, fetched ahead of the barrier it would otherwise wait behind)
+        double x_gt = 0.0;
+        if (p.mode == CST_BASE_SCB_GT && warp == 0 && lane < S && S <= 32) x_gt = __ldg(p.bcmr + video * S + lane);
         __syncthreads();
 
         // ---- scores, baseline (utils.py:292-322), rewards, per-video statistics ----
@@ -679,67 +682,115 @@ __global__ void __launch_bounds__(NW * 32, CTAS) k_score2(const ScoreParams p) {
         double inv_R = (R > 0) ? __drcp_rn((double)R) : 0.0;
         if (STAGED && bad_image) inv_R = __longlong_as_double(0x7ff8000000000000ll);   // not this build's image: NaN, loudly
         const int k_mode = p.mode;
-#pragma unroll 1
-        for (int c = threadIdx.x; c < n_local; c += NT) {
-            const double s = (sc[c] * 0.25) * inv_R * 10.0;
-            sc[c] = s;
-            if (p.scores) {
-                const bool is_greedy = c >= S;
-                p.scores[(is_greedy ? p.n_cand : 0) + video * S + (is_greedy ? c - S : c)] = s;
-            }
-        }
-        __syncthreads();
-        if (k_mode >= 0) {
-            const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
-            const double* x = (k_mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
-            if (scb) {
-                // k lowest of the row (utils.py:294-312): element i is ranked by one warp with ballots
-                // (ties by index = stable sort); low[i] = x_i if its rank < k.  k >= S keeps them all.
-                if (p.scb_k >= S) {
-#pragma unroll 1
-                    for (int i = threadIdx.x; i < S; i += NT) low[i] = x[i];
-                } else {
-#pragma unroll 1
-                    for (int i = warp; i < S; i += NW) {
-                        const double xi = x[i];
-                        int rank = 0;
-#pragma unroll 1
-                        for (int j0 = 0; j0 < S; j0 += 32) {
-                            const int j = j0 + lane;
-                            const double xj = (j < S) ? x[j] : 0.0;
-                            rank += __popc(__ballot_sync(CST_FULL, j < S && (xj < xi || (xj == xi && j < i))));
-                        }
-                        if (lane == 0) low[i] = (rank < p.scb_k) ? xi : 0.0;
+        if (S <= 32) {
+            // up to 32 captions per video (every training shape): warp 0 finishes the video by itself,
+            // lane = caption -- no further barrier, no shared-memory round trips; the sums below are the
+            // CTA-wide path's, term for term
+            if (warp == 0) {
+                const bool on = lane < S;
+                double sv = 0.0, gv = 0.0;
+                if (on) {
+                    sv = (sc[lane] * 0.25) * inv_R * 10.0;
+                    if (p.scores) p.scores[video * S + lane] = sv;
+                    if (n_local > S) {
+                        gv = (sc[S + lane] * 0.25) * inv_R * 10.0;
+                        if (p.scores) p.scores[p.n_cand + video * S + lane] = gv;
                     }
                 }
-                __syncthreads();
-            }
-            double lowsum = 0.0;
-            if (scb) {
+                if (k_mode >= 0) {
+                    const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
+                    double x = sv;
+                    if (k_mode == CST_BASE_SCB_GT) x = x_gt;
+                    double lowsum = 0.0;
+                    if (scb) {
+                        // k lowest of the row (utils.py:294-312): rank by counting, ties by index (= stable
+                        // sort); k >= S keeps them all
+                        int rank = 0;
+                        if (p.scb_k < S) {
 #pragma unroll 1
-                for (int i = lane; i < S; i += 32) lowsum += low[i];
-                lowsum = warp_sum(lowsum);                       // same fixed tree in every warp
-            }
-            const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
-#pragma unroll 1
-            for (int i = threadIdx.x; i < S; i += NT) {
-                const double r = (k_mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
-                p.reward[video * S + i] = (float)r;
-            }
-            if (warp == 0) {                                      // the video's share of the statistics
-                double am = 0.0, ab = 0.0;
-#pragma unroll 1
-                for (int i = lane; i < S; i += 32) {
-                    am += sc[i];
-                    if (k_mode == CST_BASE_GREEDY) ab += sc[S + i];
-                    if (k_mode == CST_BASE_SCB_GT) ab += x[i];
+                            for (int j = 0; j < S; ++j) {
+                                const double xj = __shfl_sync(CST_FULL, x, j);
+                                rank += (xj < x || (xj == x && j < lane)) ? 1 : 0;
+                            }
+                        }
+                        lowsum = warp_sum((on && rank < p.scb_k) ? x : 0.0);
+                    }
+                    const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
+                    if (on) p.reward[video * S + lane] = (float)((k_mode == CST_BASE_GREEDY) ? sv - gv : sv - base);
+                    const double am = warp_sum(on ? sv : 0.0);
+                    double ab = 0.0;
+                    if (k_mode == CST_BASE_GREEDY) ab = warp_sum(on ? gv : 0.0);
+                    if (k_mode == CST_BASE_SCB_GT) ab = warp_sum(on ? x : 0.0);
+                    if (k_mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
+                    if (lane == 0) {
+                        p.partials[2 * video] = am;
+                        p.partials[2 * video + 1] = ab;
+                    }
                 }
-                am = warp_sum(am);
-                ab = warp_sum(ab);
-                if (k_mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
-                if (lane == 0) {
-                    p.partials[2 * video] = am;
-                    p.partials[2 * video + 1] = ab;
+            }
+        } else {
+#pragma unroll 1
+            for (int c = threadIdx.x; c < n_local; c += NT) {
+                const double s = (sc[c] * 0.25) * inv_R * 10.0;
+                sc[c] = s;
+                if (p.scores) {
+                    const bool is_greedy = c >= S;
+                    p.scores[(is_greedy ? p.n_cand : 0) + video * S + (is_greedy ? c - S : c)] = s;
+                }
+            }
+            __syncthreads();
+            if (k_mode >= 0) {
+                const bool scb = (k_mode == CST_BASE_SCB_GT || k_mode == CST_BASE_SCB_SAMPLE);
+                const double* x = (k_mode == CST_BASE_SCB_GT) ? (p.bcmr + video * S) : sc;
+                if (scb) {
+                    // k lowest of the row (utils.py:294-312): element i is ranked by one warp with ballots
+                    // (ties by index = stable sort); low[i] = x_i if its rank < k.  k >= S keeps them all.
+                    if (p.scb_k >= S) {
+#pragma unroll 1
+                        for (int i = threadIdx.x; i < S; i += NT) low[i] = x[i];
+                    } else {
+#pragma unroll 1
+                        for (int i = warp; i < S; i += NW) {
+                            const double xi = x[i];
+                            int rank = 0;
+#pragma unroll 1
+                            for (int j0 = 0; j0 < S; j0 += 32) {
+                                const int j = j0 + lane;
+                                const double xj = (j < S) ? x[j] : 0.0;
+                                rank += __popc(__ballot_sync(CST_FULL, j < S && (xj < xi || (xj == xi && j < i))));
+                            }
+                            if (lane == 0) low[i] = (rank < p.scb_k) ? xi : 0.0;
+                        }
+                    }
+                    __syncthreads();
+                }
+                double lowsum = 0.0;
+                if (scb) {
+#pragma unroll 1
+                    for (int i = lane; i < S; i += 32) lowsum += low[i];
+                    lowsum = warp_sum(lowsum);                       // same fixed tree in every warp
+                }
+                const double base = scb ? lowsum * __drcp_rn((double)p.scb_k) : 0.0;
+#pragma unroll 1
+                for (int i = threadIdx.x; i < S; i += NT) {
+                    const double r = (k_mode == CST_BASE_GREEDY) ? sc[i] - sc[S + i] : sc[i] - base;
+                    p.reward[video * S + i] = (float)r;
+                }
+                if (warp == 0) {                                      // the video's share of the statistics
+                    double am = 0.0, ab = 0.0;
+#pragma unroll 1
+                    for (int i = lane; i < S; i += 32) {
+                        am += sc[i];
+                        if (k_mode == CST_BASE_GREEDY) ab += sc[S + i];
+                        if (k_mode == CST_BASE_SCB_GT) ab += x[i];
+                    }
+                    am = warp_sum(am);
+                    ab = warp_sum(ab);
+                    if (k_mode == CST_BASE_SCB_SAMPLE) ab = lowsum;
+                    if (lane == 0) {
+                        p.partials[2 * video] = am;
+                        p.partials[2 * video + 1] = ab;
+                    }
                 }
             }
         }
