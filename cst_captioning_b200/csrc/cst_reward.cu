@@ -918,10 +918,10 @@ extern "C" int cst_reward_cooked(const cst_df_table* table, const void* cand, co
                        scratch_bytes, stream, images, image_index, image_stride);
 }
 
-// Phase R of k_score run once per video and kept: one image per video at images_out + v * image_stride
+// The reference stages of k_score2 run once per video and kept: one image per video at images_out + v * image_stride
 // (cst_refs_cooked_bytes).  bad_rows_out (device, optional) receives the number of reference rows that
-// held ids outside [-1, 65534], plus one per video with more than refs_per_video refs (its image is
-// marked invalid).
+// held ids outside [-1, 65534], plus one per video beyond one image (more than 32 refs or 1,100 n-gram
+// instances: its image is marked invalid).
 extern "C" int cst_refs_cook(const cst_df_table* t, const void* refs, int32_t ref_dtype, int64_t n_rows,
                              int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
                              int32_t refs_per_video, int64_t n_videos, int32_t use_eos, void* images_out,

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Developer tool: device-resident timing of the bench workload's reward call only.
 
-    [CST_REWARD_LIB=...] [CST_KERNEL=1] python tools/bench_kernel.py [--videos N] [--steps K] [--int64]
+    [CST_REWARD_LIB=...] python tools/bench_kernel.py [--videos N] [--steps K] [--int64] [--mode scb*|greedy|scb]
 Prints one JSON line: ms per step, captions/s, m_score (a checksum to compare builds with).
 """
 import argparse
@@ -56,7 +56,7 @@ for _ in range(args.steps):
 b.record()
 torch.cuda.synchronize()
 ms = a.elapsed_time(b) / args.steps
-print(json.dumps({'lib': os.path.basename(cst.LIB_PATH), 'kernel': os.environ.get('CST_KERNEL', '2'),
+print(json.dumps({'lib': os.path.basename(cst.LIB_PATH),
                   'mode': args.mode, 'int64': args.int64, 'videos': args.videos, 'ms_per_step': ms,
                   'captions_per_s': args.videos * 20 / ms * 1e3, 'm_score': float(out[1]), 'b_score': float(out[2]),
                   'reward_sum_abs': float(out[0][:, 0].double().abs().sum())}))
