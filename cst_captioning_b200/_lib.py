@@ -56,6 +56,8 @@ SYMBOLS = {
                                            _vp]),
     'cst_df_sole_holders': (C.c_int, [_vp, _vp, _i32, _i64, _i32, _i64, _i32, _i64, _i32, _vp, _vp, _vp]),
     'cst_df_leave_one_out': (C.c_int, [_vp, _vp, _i32, _vp]),
+    'cst_bleu_scores': (C.c_int, _ROWS + [_vp, _vp, _vp, _i32, _vp]),
+    'cst_rouge_scores': (C.c_int, _ROWS + [_vp, _vp, _i32, _vp]),
     'cst_scb_apply': (C.c_int, [_vp, _vp, _i64, _i32, _i32, _i32, _vp, _vp, _vp, _i64, C.c_int, _vp]),
 }
 

@@ -54,8 +54,10 @@ class WordIds:
         self.on_long = on_long
         self.truncated = 0
 
-    def ids(self, sentence, keep_numbers=False):
-        toks = sentence.split()
+    def ids(self, sentence, keep_numbers=False, sep=None):
+        """``sep``: what ``str.split`` is given -- None for the scorers that cut on any white space
+        (``precook``), ``' '`` for ROUGE's ``split(" ")``, whose empty tokens are words like any other."""
+        toks = sentence.split(sep)
         if len(toks) > self.max_tokens:
             if self.on_long == 'error':
                 raise ValueError('caption of %d words exceeds the %d tokens a kernel row holds (pass '

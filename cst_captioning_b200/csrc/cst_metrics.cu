@@ -1,0 +1,474 @@
+// The other two reward scorers the reference can be run with (train.py:119-124, --eval_metric):
+// sentence BLEU (Bleu_4 is what the reward reads, utils.py:210-218, 276-282) and ROUGE-L, on the same
+// token rows, canonicalisation and candidate -> video map as the CIDEr-D path.
+// Both restate pycocoevalcap (bleu/bleu_scorer.py, rouge/rouge.py), which the reference imports from an
+// un-vendored checkout; METEOR there is a Java program and has no counterpart here.
+//
+// One CTA of 8 warps per video, like k_score2, built from its helpers (cst_rows.cuh):
+//
+//   k_bleu   "the candidates own the table, the references stream through it".  BLEU needs, per candidate
+//            n-gram, the LARGEST count of that n-gram in any one reference -- a maximum, not a sum, so the
+//            reference chunks of k_score2 would not add up.  Turned round it needs no chunks at all: the
+//            n-grams of a batch of candidates (<= 32 rows, <= 832 instances) go into the shared-memory
+//            table first, then reference rows pass through in stages of any number, each instance
+//            raising the maximum of the slot it finds (most find nothing: one probe), and the closest
+//            reference length per candidate is kept on the way.  Integer work end to end -- counts,
+//            maxima and clipped sums are exact -- followed by four pow() and one exp() per candidate.
+//   k_rouge  LCS of every (candidate, reference) pair with the bit-vector recurrence (a reference of up to
+//            32 tokens is one machine word): V' = (V + (V & M)) | (V & ~M), LCS = zeros of V, where M marks
+//            the reference positions holding the candidate's token.  The masks come from a small
+//            shared-memory table keyed by (token, reference), filled once per batch of references; a
+//            thread owns a pair.  Precision / recall maxima are integer / IEEE-ordered atomics, the
+//            F-measure is evaluated in the scorer's own operation order without contraction: bit-exact.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "cst_common.cuh"
+#include "cst_internal.h"
+#include "cst_rows.cuh"
+
+#define MT_WARPS 8
+#define MT_THREADS (MT_WARPS * 32)
+#define MT_LIST_CAP 832
+#define MT_TAB_SLOTS 1193u            /* >= the instances of one candidate batch (MT_LIST_CAP), prime */
+#define MT_CTOK_U16 (CST2_ROWS * CST2_TOK_STRIDE + 8)
+#define RG_SLOTS 2048u                /* (token, reference) pairs of one batch of references: <= 1024 */
+#define RG_EMPTY 0xffffffffu
+
+struct RowsView {
+    const void* cand;
+    const void* greedy;      // second row set of the same geometry (scored after the first), or NULL
+    const void* refs;
+    const int64_t* ref_offsets;
+    int64_t n_cand, n_videos;
+    int cand_esz, ref_esz, cand_width, ref_width;
+    u32 pitch_c, pitch_r;
+    int refs_per_video, cands_per_video, use_eos;
+    u32* bad_out;
+};
+
+// rows [first, first + n) of one set -> canonical token codes + lengths (warp per row).  Candidate rows
+// of a video: local index c < split is a sampled row, c >= split the greedy row c - split.
+__device__ __forceinline__ void mt_load_rows(const char* base, const char* base2, int split, int first, int n,
+                                             u32 pitch, int esz, int width, int use_eos, u16* ctok, int* sL,
+                                             int warp, int lane) {
+#pragma unroll 2
+    for (int r = warp; r < n; r += MT_WARPS) {
+        int c = first + r;
+        const char* src = base;
+        if (c >= split) {
+            c -= split;
+            src = base2;
+        }
+        const char* tok = src + ((unsigned long long)(u32)c * (unsigned long long)pitch + (u32)(lane * esz));
+        u32 v = 0u;
+        if (lane < width) {
+            if (esz == 4) {
+                v = (u32)__ldcs(reinterpret_cast<const int*>(tok)) + 1u;
+            } else if (esz == 8) {
+                const long long w = __ldcs(reinterpret_cast<const long long*>(tok));
+                v = (w < -1 || w > 65534) ? 0xffffffffu : (u32)w + 1u;
+            } else {
+                v = (u32)(int)__ldcs(reinterpret_cast<const short*>(tok)) + 1u;
+            }
+        }
+        const int res = v2_canon(v, use_eos, lane, ctok + r * CST2_TOK_STRIDE);
+        if (lane == 0) sL[r] = res;
+    }
+}
+
+// n-gram instances of the batch's rows into `list` (see v2_emit): two short rows per warp
+__device__ __forceinline__ void mt_emit_rows(const u16* ctok, const V2Scan& sb, uint4* list, int warp, int lane) {
+    const int nfit = sb.nfit;
+#pragma unroll 1
+    for (int pair = warp; 2 * pair < nfit; pair += MT_WARPS) {
+        const int ra = 2 * pair, rb = ra + 1;
+        const int La = __shfl_sync(CST_FULL, sb.L, ra);
+        const int Lb = (rb < nfit) ? __shfl_sync(CST_FULL, sb.L, rb & 31) : 0;
+        if (La <= 16 && Lb <= 16) {
+            const bool second = (lane >> 4) != 0;
+            v2_emit<16>(ctok, second ? (rb & 31) : ra, second ? Lb : La, sb, list, lane);
+        } else {
+#pragma unroll 1
+            for (int q = 0; q < 2; ++q) {
+                const int Lq = q ? Lb : La;
+                if (Lq > 0) v2_emit<32>(ctok, ra + q, Lq, sb, list, lane);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void mt_video_refs(const RowsView& p, int64_t video, int64_t& r0, int64_t& r1) {
+    if (p.ref_offsets) {
+        r0 = p.ref_offsets[video];
+        r1 = p.ref_offsets[video + 1];
+    } else {
+        r0 = video * p.refs_per_video;
+        r1 = r0 + p.refs_per_video;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// BLEU
+// ---------------------------------------------------------------------------
+#define BL_OFF_LISTC ((size_t)MT_TAB_SLOTS * sizeof(VidSlot))
+#define BL_OFF_LISTR (BL_OFF_LISTC + (size_t)MT_LIST_CAP * sizeof(uint4))
+#define BL_OFF_CTOKC (BL_OFF_LISTR + (size_t)MT_LIST_CAP * sizeof(uint4))
+#define BL_OFF_CTOKR (BL_OFF_CTOKC + MT_CTOK_U16 * sizeof(u16))
+#define BL_SMEM (BL_OFF_CTOKR + MT_CTOK_U16 * sizeof(u16))
+
+// bleu_out [4][n_total] (order-major: row 3 is the BLEU-4 vector the reward reads), comps_out [n_total][6]
+// = testlen, reflen, correct[4] (what the corpus-level score adds up; guess[k] = max(testlen - k, 0)).
+__global__ void __launch_bounds__(MT_THREADS, 4) k_bleu(const RowsView p, double* __restrict__ bleu_out,
+                                                        int* __restrict__ comps_out) {
+    constexpr u32 T = MT_TAB_SLOTS;
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int sLc[CST2_ROWS], sLr[CST2_ROWS];
+    __shared__ int s_correct[CST2_ROWS][4];
+    VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
+    uint4* listC = reinterpret_cast<uint4*>(smem + BL_OFF_LISTC);
+    uint4* listR = reinterpret_cast<uint4*>(smem + BL_OFF_LISTR);
+    u16* ctokC = reinterpret_cast<u16*>(smem + BL_OFF_CTOKC);
+    u16* ctokR = reinterpret_cast<u16*>(smem + BL_OFF_CTOKR);
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
+    const int S = p.cands_per_video;
+    const int n_local = p.greedy ? 2 * S : S;
+    const int64_t n_total = p.greedy ? 2 * p.n_cand : p.n_cand;
+
+#pragma unroll 1
+    for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
+        int64_t r0, r1;
+        mt_video_refs(p, video, r0, r1);
+        const char* cbase = reinterpret_cast<const char*>(p.cand) + (size_t)(video * S) * p.pitch_c;
+        const char* gbase = reinterpret_cast<const char*>(p.greedy) + (size_t)(video * S) * p.pitch_c;
+        u32 bad_rows = 0;
+        bool first_batch = true;
+#pragma unroll 1
+        for (int cb = 0; cb < n_local;) {
+            // ---- the candidate batch: rows -> instances -> table (counts start at 0) ----
+            {
+                uint4* z = reinterpret_cast<uint4*>(tab);
+#pragma unroll 2
+                for (u32 i = threadIdx.x; i < T; i += MT_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+                if (threadIdx.x < CST2_ROWS * 4) (&s_correct[0][0])[threadIdx.x] = 0;
+            }
+            const int n_try = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
+            mt_load_rows(cbase, gbase, S, cb, n_try, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
+            __syncthreads();
+            const V2Scan sc = v2_scan(sLc, n_try, MT_LIST_CAP, lane);
+            const int nC = sc.nfit;
+            if (warp == 0 && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
+            mt_emit_rows(ctokC, sc, listC, warp, lane);
+            __syncthreads();
+#pragma unroll 1
+            for (int i = (int)threadIdx.x; i < sc.n_ent; i += MT_THREADS) {
+                const uint4 e = listC[i];
+                if (e.z != 0u) {
+                    const u64 key = (u64)e.x | ((u64)e.y << 32);
+                    listC[i].w = v2_insert<T>(tab, cst_hash(key), key);
+                }
+            }
+            // closest reference length of the lane's candidate (warp 0): (|l - testlen|, l) smallest
+            u32 best = 0xffffffffu;
+            const int Lh = sc.L;                     // lane h: testlen of candidate row h
+            // ---- the references stream through ----
+#pragma unroll 1
+            for (int64_t rb = r0; rb < r1;) {
+                const int left = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
+                mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, left,
+                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
+                __syncthreads();                     // (also: every candidate key is in the table by now)
+                const V2Scan sr = v2_scan(sLr, left, MT_LIST_CAP, lane);
+                const int nR = sr.nfit;
+                if (warp == 0 && lane < nR && first_batch) bad_rows += (u32)(sLr[lane] >> 8);
+                mt_emit_rows(ctokR, sr, listR, warp, lane);
+                if (warp == 0) {
+#pragma unroll 1
+                    for (int j = 0; j < nR; ++j) {
+                        const int l = __shfl_sync(CST_FULL, sr.L, j);
+                        const int d = (l > Lh) ? l - Lh : Lh - l;
+                        const u32 cand = ((u32)d << 8) | (u32)l;
+                        best = cand < best ? cand : best;
+                    }
+                }
+                __syncthreads();
+#pragma unroll 1
+                for (int i = (int)threadIdx.x; i < sr.n_ent; i += MT_THREADS) {
+                    const uint4 e = listR[i];
+                    if (e.z != 0u) {
+                        const u64 key = (u64)e.x | ((u64)e.y << 32);
+                        const int idx = v2_find<T, false>(tab, cst_hash(key), key);
+                        if (idx >= 0) atomicMax(&tab[idx].P, e.z >> 8);       // cook_refs: maxcounts
+                    }
+                }
+                rb += nR;
+                __syncthreads();                     // listR, ctokR, sLr are reused; the maxima are final
+            }
+            if (r0 >= r1) __syncthreads();           // (no references: the inserts still have to land)
+            // ---- clipped counts: min(count in the candidate, largest count in a reference) ----
+#pragma unroll 1
+            for (int i = (int)threadIdx.x; i < sc.n_ent; i += MT_THREADS) {
+                const uint4 e = listC[i];
+                if (e.z != 0u) {
+                    const u32 tf = e.z >> 8, mx = tab[e.w].P;
+                    const u32 c = tf < mx ? tf : mx;
+                    if (c) atomicAdd(&s_correct[e.z & 31u][(e.z >> 5) & 3u], (int)c);
+                }
+            }
+            __syncthreads();
+            // ---- BleuScorer.compute_score, the per-sentence part ----
+            if (warp == 0 && lane < nC) {
+                const int c = cb + lane;
+                const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
+                const int testlen = Lh;
+                const int reflen = (best == 0xffffffffu) ? 0 : (int)(best & 0xffu);
+                const double small = 1e-9, tiny = 1e-15;
+                const double ratio = ((double)testlen + tiny) / ((double)reflen + small);
+                const double bp = (ratio < 1.0) ? exp(1.0 - 1.0 / ratio) : 1.0;
+                double bleu = 1.0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int guess = testlen > k ? testlen - k : 0;
+                    bleu *= ((double)s_correct[lane][k] + tiny) / ((double)guess + small);
+                    double b = (k == 0) ? bleu : (k == 1) ? sqrt(bleu) : pow(bleu, 1.0 / (double)(k + 1));
+                    if (ratio < 1.0) b *= bp;
+                    bleu_out[(size_t)k * (size_t)n_total + (size_t)out] = b;
+                }
+                if (comps_out) {
+                    int* q = comps_out + (size_t)out * 6;
+                    q[0] = testlen;
+                    q[1] = reflen;
+                    q[2] = s_correct[lane][0];
+                    q[3] = s_correct[lane][1];
+                    q[4] = s_correct[lane][2];
+                    q[5] = s_correct[lane][3];
+                }
+            }
+            cb += nC;
+            first_batch = false;
+            __syncthreads();
+        }
+        if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// ROUGE-L
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ u32 rg_home(u32 key) { return (key * 0x9E3779B1u) >> 21; }   // 11 bits: RG_SLOTS
+
+__device__ __forceinline__ u32 rg_find(const uint2* tab, u32 key) {
+    u32 idx = rg_home(key);
+#pragma unroll 1
+    for (;;) {
+        const uint2 s = tab[idx];
+        if (s.x == key) return s.y;
+        if (s.x == RG_EMPTY) return 0u;
+        idx = (idx + 1u) & (RG_SLOTS - 1u);
+    }
+}
+
+__global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, double* __restrict__ scores) {
+    __shared__ __align__(16) uint2 tab[RG_SLOTS];
+    __shared__ __align__(16) u16 ctokC[MT_CTOK_U16];
+    __shared__ __align__(16) u16 ctokR[MT_CTOK_U16];
+    __shared__ int sLc[CST2_ROWS], sLr[CST2_ROWS];
+    __shared__ int s_lcs[CST2_ROWS];
+    __shared__ unsigned long long s_rec[CST2_ROWS];
+    const int lane = threadIdx.x & 31;
+    const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
+    const int S = p.cands_per_video;
+    const int n_local = p.greedy ? 2 * S : S;
+
+#pragma unroll 1
+    for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
+        int64_t r0, r1;
+        mt_video_refs(p, video, r0, r1);
+        const char* cbase = reinterpret_cast<const char*>(p.cand) + (size_t)(video * S) * p.pitch_c;
+        const char* gbase = reinterpret_cast<const char*>(p.greedy) + (size_t)(video * S) * p.pitch_c;
+        u32 bad_rows = 0;
+#pragma unroll 1
+        for (int cb = 0; cb < n_local; cb += CST2_ROWS) {
+            const int nC = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
+            mt_load_rows(cbase, gbase, S, cb, nC, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
+            if (threadIdx.x < CST2_ROWS) {
+                s_lcs[threadIdx.x] = 0;
+                s_rec[threadIdx.x] = 0ull;
+            }
+            __syncthreads();
+            if (warp == 0 && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
+#pragma unroll 1
+            for (int64_t rb = r0; rb < r1; rb += CST2_ROWS) {
+                const int nR = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
+#pragma unroll 2
+                for (u32 i = threadIdx.x; i < RG_SLOTS; i += MT_THREADS) tab[i] = make_uint2(RG_EMPTY, 0u);
+                mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, nR,
+                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
+                __syncthreads();
+                if (warp == 0 && cb == 0 && lane < nR) bad_rows += (u32)(sLr[lane] >> 8);
+                // positions of every token of every reference: mask of (token, reference).  An empty
+                // sentence is ONE empty token (split(" ")): code 0, which no word has.
+#pragma unroll 1
+                for (int t = (int)threadIdx.x; t < nR * 32; t += MT_THREADS) {
+                    const int r = t >> 5, j = t & 31;
+                    const int L = sLr[r] & 0xff;
+                    if (j < (L > 0 ? L : 1)) {
+                        const u32 key = (L > 0 ? (u32)ctokR[r * CST2_TOK_STRIDE + j] : 0u) | ((u32)r << 16);
+                        u32 idx = rg_home(key);
+#pragma unroll 1
+                        for (;;) {
+                            const u32 cur = *reinterpret_cast<volatile u32*>(&tab[idx].x);
+                            if (cur == key) break;
+                            if (cur == RG_EMPTY) {
+                                const u32 old = atomicCAS(&tab[idx].x, RG_EMPTY, key);
+                                if (old == RG_EMPTY || old == key) break;
+                            }
+                            idx = (idx + 1u) & (RG_SLOTS - 1u);
+                        }
+                        atomicOr(&tab[idx].y, 1u << j);
+                    }
+                }
+                __syncthreads();
+                // a thread per (candidate, reference): my_lcs as the bit-vector recurrence
+#pragma unroll 1
+                for (int t = (int)threadIdx.x; t < nC * nR; t += MT_THREADS) {
+                    const int h = t / nR, r = t - h * nR;
+                    const int Lh = sLc[h] & 0xff, Lr = sLr[r] & 0xff;
+                    const u32 rkey = (u32)r << 16;
+                    u32 V = 0xffffffffu;
+                    const u16* ct = ctokC + h * CST2_TOK_STRIDE;
+                    const int steps = Lh > 0 ? Lh : 1;
+#pragma unroll 1
+                    for (int i = 0; i < steps; ++i) {
+                        const u32 M = rg_find(tab, (Lh > 0 ? (u32)ct[i] : 0u) | rkey);
+                        const u32 U = V & M;
+                        V = (V + U) | (V - U);
+                    }
+                    const int lenr = Lr > 0 ? Lr : 1;
+                    const int lcs = __popc(~V & (lenr >= 32 ? 0xffffffffu : ((1u << lenr) - 1u)));
+                    atomicMax(&s_lcs[h], lcs);                                   // prec = lcs / len(candidate)
+                    const double rec = (double)lcs / (double)lenr;               // rec  = lcs / len(reference)
+                    atomicMax(&s_rec[h], (unsigned long long)__double_as_longlong(rec));   // (>= 0: bit order = value order)
+                }
+                __syncthreads();
+            }
+            // Rouge.calc_score: F-measure of the two maxima, in the scorer's operation order
+            if (threadIdx.x < nC) {
+                const int h = (int)threadIdx.x;
+                const int c = cb + h;
+                const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
+                const int Lh = sLc[h] & 0xff;
+                const double prec = (double)s_lcs[h] / (double)(Lh > 0 ? Lh : 1);
+                const double rec = __longlong_as_double((long long)s_rec[h]);
+                const double beta2 = 1.2 * 1.2;
+                double score = 0.0;
+                if (prec != 0.0 && rec != 0.0)
+                    score = __ddiv_rn(__dmul_rn(__dmul_rn(__dadd_rn(1.0, beta2), prec), rec),
+                                      __dadd_rn(rec, __dmul_rn(beta2, prec)));
+                scores[out] = score;
+            }
+            __syncthreads();
+        }
+        if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+static int mt_dtype_bytes(int dtype) {
+    return dtype == CST_DTYPE_I32 ? 4 : dtype == CST_DTYPE_I64 ? 8 : dtype == CST_DTYPE_I16 ? 2 : 0;
+}
+
+static int mt_view(const char* who, RowsView& p, const void* cand, const void* greedy, int32_t cand_dtype,
+                   int64_t n_cand, int32_t cand_width, int64_t cand_stride, const void* refs, int32_t ref_dtype,
+                   int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets, int32_t refs_per_video,
+                   int64_t n_videos, int32_t cands_per_video, int32_t use_eos, uint32_t* bad_rows_out) {
+    if (n_cand < 0 || n_videos < 0 || cands_per_video < 1) return cst_fail(CST_E_ARG, "%s: negative size", who);
+    if (n_cand != n_videos * (int64_t)cands_per_video)
+        return cst_fail(CST_E_ARG, "%s: n_cand (%lld) != n_videos (%lld) * cands_per_video (%d)", who, (long long)n_cand,
+                        (long long)n_videos, cands_per_video);
+    if (cand_width < 1 || cand_width > CST_MAX_ROW_WIDTH || ref_width < 1 || ref_width > CST_MAX_ROW_WIDTH)
+        return cst_fail(CST_E_RANGE, "%s: row widths %d/%d outside [1, %d]", who, cand_width, ref_width, CST_MAX_ROW_WIDTH);
+    if (cand_stride < cand_width || ref_stride < ref_width) return cst_fail(CST_E_ARG, "%s: stride < width", who);
+    const int ce = mt_dtype_bytes(cand_dtype), re = mt_dtype_bytes(ref_dtype);
+    if (!ce || !re) return cst_fail(CST_E_ARG, "%s: bad dtype", who);
+    if (refs_per_video < 0 || (refs_per_video == 0 && !ref_offsets))
+        return cst_fail(CST_E_ARG, "%s: refs_per_video must be > 0", who);
+    if (cands_per_video > 4096) return cst_fail(CST_E_RANGE, "%s: cands_per_video %d > 4096", who, cands_per_video);
+    if ((uint64_t)cand_stride * (uint64_t)ce > 0xffffffffull || (uint64_t)ref_stride * (uint64_t)re > 0xffffffffull)
+        return cst_fail(CST_E_RANGE, "%s: row pitch beyond 4 GiB", who);
+    if (n_cand > 0 && (!cand || !refs)) return cst_fail(CST_E_ARG, "%s: NULL rows", who);
+    memset(&p, 0, sizeof(p));
+    p.cand = cand;
+    p.greedy = greedy;
+    p.refs = refs;
+    p.ref_offsets = ref_offsets;
+    p.n_cand = n_cand;
+    p.n_videos = n_videos;
+    p.cand_esz = ce;
+    p.ref_esz = re;
+    p.cand_width = cand_width;
+    p.ref_width = ref_width;
+    p.pitch_c = (u32)((uint64_t)cand_stride * (uint64_t)ce);
+    p.pitch_r = (u32)((uint64_t)ref_stride * (uint64_t)re);
+    p.refs_per_video = refs_per_video;
+    p.cands_per_video = cands_per_video;
+    p.use_eos = use_eos ? 1 : 0;
+    p.bad_out = bad_rows_out;
+    return CST_OK;
+}
+
+static unsigned mt_grid(int device, int64_t n_videos, int ctas_per_sm) {
+    int sms = 148;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms < 1) sms = 148;
+    // (the error, if any, is sticky-free: a failed attribute query leaves no pending error)
+    const int64_t full = (int64_t)sms * ctas_per_sm * 8;      // several waves: CTAs of uneven videos even out
+    return (unsigned)(n_videos < full ? n_videos : full);
+}
+
+extern "C" int cst_bleu_scores(const void* cand, const void* greedy, int32_t cand_dtype, int64_t n_cand,
+                               int32_t cand_width, int64_t cand_stride, const void* refs, int32_t ref_dtype,
+                               int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
+                               int32_t refs_per_video, int64_t n_videos, int32_t cands_per_video, int32_t use_eos,
+                               double* bleu_out, int32_t* comps_out, uint32_t* bad_rows_out, int32_t device,
+                               void* stream) {
+    RowsView p;
+    int rc = mt_view("cst_bleu_scores", p, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
+                     ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, bad_rows_out);
+    if (rc != CST_OK) return rc;
+    if (n_cand == 0) return CST_OK;
+    if (!bleu_out) return cst_fail(CST_E_ARG, "cst_bleu_scores: NULL output");
+    CstDeviceGuard guard(device);
+    if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_bleu_scores: cannot select device %d", device);
+    static bool attr_set[64] = {false};
+    if (device < 0 || device >= 64 || !attr_set[device]) {
+        CST_CUDA_TRY(cudaFuncSetAttribute(k_bleu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BL_SMEM));
+        if (device >= 0 && device < 64) attr_set[device] = true;     // (a constant: racing threads set the same value)
+    }
+    k_bleu<<<mt_grid(device, n_videos, 4), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
+    cst_count_launch();
+    CST_CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}
+
+extern "C" int cst_rouge_scores(const void* cand, const void* greedy, int32_t cand_dtype, int64_t n_cand,
+                                int32_t cand_width, int64_t cand_stride, const void* refs, int32_t ref_dtype,
+                                int32_t ref_width, int64_t ref_stride, const int64_t* ref_offsets,
+                                int32_t refs_per_video, int64_t n_videos, int32_t cands_per_video, int32_t use_eos,
+                                double* scores_out, uint32_t* bad_rows_out, int32_t device, void* stream) {
+    RowsView p;
+    int rc = mt_view("cst_rouge_scores", p, cand, greedy, cand_dtype, n_cand, cand_width, cand_stride, refs, ref_dtype,
+                     ref_width, ref_stride, ref_offsets, refs_per_video, n_videos, cands_per_video, use_eos, bad_rows_out);
+    if (rc != CST_OK) return rc;
+    if (n_cand == 0) return CST_OK;
+    if (!scores_out) return cst_fail(CST_E_ARG, "cst_rouge_scores: NULL output");
+    CstDeviceGuard guard(device);
+    if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_rouge_scores: cannot select device %d", device);
+    k_rouge<<<mt_grid(device, n_videos, 6), MT_THREADS, 0, (cudaStream_t)stream>>>(p, scores_out);
+    cst_count_launch();
+    CST_CUDA_TRY(cudaGetLastError());
+    return CST_OK;
+}

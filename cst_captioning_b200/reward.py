@@ -323,17 +323,47 @@ def _finish(reward, stats, width):
 
 
 def _need_scorer(bcmr_scorer):
-    if not isinstance(bcmr_scorer, CiderD):
-        raise TypeError('the GPU reward path implements the CiderD scorer only '
-                        '(utils.py:194,260 dispatch); got %r' % type(bcmr_scorer).__name__)
+    from .metrics import _RowScorer
+    if not isinstance(bcmr_scorer, (CiderD, _RowScorer)):
+        raise TypeError('the GPU reward path implements the CiderD, Bleu and Rouge scorers '
+                        '(train.py:119-124; utils.py:194,260 dispatch); got %r' % type(bcmr_scorer).__name__)
     return bcmr_scorer
+
+
+def _scorer_device(scorer):
+    return scorer.table.device if isinstance(scorer, CiderD) else scorer.device
+
+
+def _reward_from_scores(scorer, sampled, greedy, refs, cands_per_video, use_eos, mode, seq_per_img, k, bcmr):
+    """Bleu / Rouge (train.py:119-124): their scores come from a kernel of their own; the baseline
+    block of utils.py:219-224, 292-322 is then the standalone ``cst_scb_apply`` on the score vector
+    (for ``Bleu`` the BLEU-4 list, utils.py:210-213, 276-279)."""
+    if isinstance(refs, CookedRefs):
+        raise TypeError('staged references hold the CIDEr-D half of the scoring: pass the rows (RefSet) to %s'
+                        % type(scorer).__name__)
+    dev = scorer.device
+    n = sampled.shape[0]
+    reward = torch.empty(n, dtype=torch.float32, device=dev)
+    if n == 0:
+        return reward, torch.zeros(_lib.N_STATS, dtype=torch.float64, device=dev)
+    if n % seq_per_img:
+        raise ValueError('cannot reshape %d scores into rows of %d' % (n, seq_per_img))
+    stats = torch.empty(_lib.N_STATS, dtype=torch.float64, device=dev)
+    scores = scorer.score_rows(sampled, refs, cands_per_video, use_eos, greedy=greedy)
+    other = scores[n:] if greedy is not None else bcmr
+    stream = _stream(dev)
+    scratch = _scratch_for(dev, n // seq_per_img, stream)
+    check(lib.cst_scb_apply(scores.data_ptr(), other.data_ptr() if other is not None else None, n // seq_per_img,
+                            seq_per_img, mode, k, reward.data_ptr(), stats.data_ptr(), scratch.data_ptr(),
+                            scratch.numel(), dev.index, stream))
+    return reward, stats
 
 
 def get_self_critical_reward(model_res, greedy_res, data_gts, bcmr_scorer, expand_feat=0,
                              seq_per_img=20, use_eos=0, return_stats=False):
     """``utils.py:169-226``: reward = CIDEr-D(sampled) - CIDEr-D(greedy)."""
     scorer = _need_scorer(bcmr_scorer)
-    dev = scorer.table.device
+    dev = _scorer_device(scorer)
     sampled = _rows_on_device(model_res, dev)
     greedy = _rows_on_device(greedy_res, dev)
     if greedy.shape[0] != sampled.shape[0]:
@@ -347,8 +377,12 @@ def get_self_critical_reward(model_res, greedy_res, data_gts, bcmr_scorer, expan
         greedy = torch.nn.functional.pad(greedy.to(dt), (0, w - greedy.shape[1])).contiguous()
     refs = RefSet.coerce(data_gts, dev)
     per_video = seq_per_img if expand_feat == 1 else 1
-    reward, stats, _ = _launch_reward(scorer, sampled, greedy, refs, per_video, use_eos,
-                                      _lib.BASE_GREEDY, per_video, 0, None, False)
+    if isinstance(scorer, CiderD):
+        reward, stats, _ = _launch_reward(scorer, sampled, greedy, refs, per_video, use_eos,
+                                          _lib.BASE_GREEDY, per_video, 0, None, False)
+    else:
+        reward, stats = _reward_from_scores(scorer, sampled, greedy, refs, per_video, use_eos, _lib.BASE_GREEDY,
+                                            per_video, 0, None)
     out = _finish(reward, stats, model_res.shape[1])
     return out + (stats,) if return_stats else out
 
@@ -359,7 +393,7 @@ def get_cst_reward(model_res, data_gts, bcmr_scorer, bcmrscores=None, expand_fea
     scores ``bcmrscores``, 2 = from the model samples' own scores; the baseline is
     the mean of the ``scb_captions`` lowest scores of the video's row."""
     scorer = _need_scorer(bcmr_scorer)
-    dev = scorer.table.device
+    dev = _scorer_device(scorer)
     width = model_res.shape[1]
 
     if scb_captions > 0:
@@ -388,9 +422,13 @@ def get_cst_reward(model_res, data_gts, bcmr_scorer, bcmrscores=None, expand_fea
         per_video = seq_per_img if expand_feat == 1 else 1
         if bcmr is not None and mode == _lib.BASE_SCB_GT and bcmr.numel() != sampled.shape[0]:
             raise ValueError('bcmrscores must hold one score per sampled caption')
-        reward, stats, _ = _launch_reward(scorer, sampled, None, refs, per_video, use_eos, mode,
-                                          seq_per_img, k, bcmr if mode == _lib.BASE_SCB_GT else None,
-                                          False)
+        gt = bcmr if mode == _lib.BASE_SCB_GT else None
+        if isinstance(scorer, CiderD):
+            reward, stats, _ = _launch_reward(scorer, sampled, None, refs, per_video, use_eos, mode,
+                                              seq_per_img, k, gt, False)
+        else:
+            reward, stats = _reward_from_scores(scorer, sampled, None, refs, per_video, use_eos, mode,
+                                                seq_per_img, k, gt)
     else:
         # WXE (utils.py:286-288): the precomputed consensus scores ARE the scores
         if bcmr.dim() != 2 or bcmr.shape[1] != seq_per_img:

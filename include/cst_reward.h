@@ -308,6 +308,42 @@ int cst_scb_apply(const double* scores, const double* other, int64_t n_rows,
                   float* reward_out, double* stats_out, void* scratch,
                   int64_t scratch_bytes, int device, void* stream);
 
+/* ---- the other reward scorers ------------------------------------------
+ * train.py:119-124 picks the reward scorer by --eval_metric: 'CIDEr' (everything above), 'Bleu_4',
+ * 'ROUGE_L' or 'METEOR'.  These two entry points replace Bleu().compute_score / Rouge().compute_score
+ * of pycocoevalcap as called at utils.py:208, 274 (dict protocol: res[i] = [candidate string]) together
+ * with the string building around them; rows, canonicalisation, the candidate -> video map and the
+ * greedy row set are those of cst_cider_scores.  The rewards follow with cst_scb_apply on the score
+ * vector (BLEU: row 3 of bleu_out, the Bleu_4 list -- utils.py:210-213, 276-279).  METEOR is a Java
+ * program in the reference's checkout: no counterpart.
+ *
+ *   bleu_out    [dev] float64 [4][n_total], n_total = n_cand (2 n_cand with greedy rows, sampled first):
+ *               per-sentence BLEU-1..4 of BleuScorer.compute_score(option='closest')
+ *   comps_out   [dev] int32 [n_total][6] or NULL: testlen, closest reflen, clipped-correct counts of
+ *               orders 1..4 -- the sums the corpus-level score is made of (guess_k = max(testlen-k+1, 0))
+ *   scores_out  [dev] float64 [n_total]: Rouge.calc_score per candidate (beta = 1.2), bit-exact
+ *   bad_rows_out [dev] uint32 or NULL: incremented by the number of rows holding ids outside
+ *               [-1, 65534] (scored as if the bad id ended the caption)
+ * Any number of references per video (they stream through in batches of 32); rows of at most 32
+ * tokens.  A video without references scores as if its reference lengths were 0 (the reference
+ * scorers raise there). */
+int cst_bleu_scores(const void* cand, const void* greedy, int32_t cand_dtype,
+                    int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                    const void* refs, int32_t ref_dtype, int32_t ref_width,
+                    int64_t ref_stride, const int64_t* ref_offsets,
+                    int32_t refs_per_video, int64_t n_videos,
+                    int32_t cands_per_video, int32_t use_eos,
+                    double* bleu_out, int32_t* comps_out, uint32_t* bad_rows_out,
+                    int32_t device, void* stream);
+int cst_rouge_scores(const void* cand, const void* greedy, int32_t cand_dtype,
+                     int64_t n_cand, int32_t cand_width, int64_t cand_stride,
+                     const void* refs, int32_t ref_dtype, int32_t ref_width,
+                     int64_t ref_stride, const int64_t* ref_offsets,
+                     int32_t refs_per_video, int64_t n_videos,
+                     int32_t cands_per_video, int32_t use_eos,
+                     double* scores_out, uint32_t* bad_rows_out,
+                     int32_t device, void* stream);
+
 /* ---- fused consumer of the reward -------------------------------
  * Replaces RewardCriterion.forward (model.py:12-23) and its autograd backward as
  * called at train.py:206-210: loss = sum(-logprobs * reward * mask) / sum(mask) with

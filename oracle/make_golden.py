@@ -43,8 +43,9 @@ def import_reference():
         sys.modules[name] = m
         return m
 
-    class _Absent:  # Bleu/Rouge/Meteor/COCO are never instantiated on the path
+    class _Absent:  # Meteor/COCO are never instantiated on the path
         pass
+    from oracle import bleu_rouge_oracle
 
     stub('pyciderevalcap')
     stub('pyciderevalcap.ciderD')
@@ -53,9 +54,12 @@ def import_reference():
     stub('pycocotools.coco', COCO=_Absent)
     stub('pycocoevalcap')
     stub('pycocoevalcap.eval', COCOEvalCap=_Absent)
-    for sub, cls in (('bleu', 'Bleu'), ('rouge', 'Rouge'), ('meteor', 'Meteor')):
+    # (the restated Bleu / Rouge, so that utils.py:211,277 `isinstance(bcmr_scorer, Bleu)` fires for
+    # oracle/make_golden_metrics.py; the CIDEr fixtures below never touch them)
+    for sub, cls, impl in (('bleu', 'Bleu', bleu_rouge_oracle.Bleu), ('rouge', 'Rouge', bleu_rouge_oracle.Rouge),
+                           ('meteor', 'Meteor', _Absent)):
         stub('pycocoevalcap.' + sub)
-        stub('pycocoevalcap.%s.%s' % (sub, sub), **{cls: type(cls, (), {})})
+        stub('pycocoevalcap.%s.%s' % (sub, sub), **{cls: impl})
     sys.path.insert(0, REF)
     import utils as ref_utils
     import compute_ciderdf as ref_df

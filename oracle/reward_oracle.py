@@ -56,16 +56,25 @@ def _video_of(i, n_cand, expand_feat, seq_per_img):
 def score_rows(model_rows, data_gts, scorer, expand_feat, seq_per_img, use_eos,
                n_cand=None):
     """Scores of every row of ``model_rows`` against its video's refs through
-    ``scorer.compute_score`` (the CiderD list-of-dict protocol,
-    ``utils.py:194-198, 260-264``)."""
-    assert isinstance(scorer, CiderD)
+    ``scorer.compute_score``: the list-of-dict protocol for ``CiderD``
+    (``utils.py:194-198, 260-264``), the dict protocol for any other scorer;
+    of ``Bleu``'s four score lists the last one, BLEU-4, counts
+    (``utils.py:210-218, 276-282``)."""
+    from .bleu_rouge_oracle import Bleu
     hyp, refs = _strings_for(model_rows, data_gts, use_eos)
     total = len(hyp)
     n_cand = total if n_cand is None else n_cand
-    res = [{'image_id': i, 'caption': hyp[i]} for i in range(total)]
+    if isinstance(scorer, CiderD):
+        res = [{'image_id': i, 'caption': hyp[i]} for i in range(total)]
+    else:
+        res = {i: hyp[i] for i in range(total)}
     gts = {i: refs[_video_of(i, n_cand, expand_feat, seq_per_img)]
            for i in range(total)}
     _, scores = scorer.compute_score(gts, res)
+    if isinstance(scorer, Bleu):
+        scores = scores[-1]
+    if type(scores) == list:
+        scores = np.array(scores)
     return scores
 
 

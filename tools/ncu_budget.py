@@ -4,7 +4,7 @@
     python tools/ncu_budget.py gpurun_out/prof_r2d.ncu-rep [videos]
 
 Reads the source page of the report (``--import-source on``) and adds up the per-line counters
-over the line ranges of cst_score2.cuh that make up each stage (found by their anchor text, so
+over the line ranges of cst_score2.cuh / cst_rows.cuh that make up each stage (found by their anchor text, so
 the table follows the source).  Output: share of executed warp instructions, instructions per
 video, share of stall samples, active threads per instruction.
 """
@@ -15,16 +15,18 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-SRC = os.path.join(ROOT, 'cst_captioning_b200', 'csrc', 'cst_score2.cuh')
+CSRC = os.path.join(ROOT, 'cst_captioning_b200', 'csrc')
 
-# (category, anchor that starts it) in file order; a category runs to the next anchor
-ANCHORS = [
+# (category, anchor that starts it) in file order; a category runs to the next anchor of its file
+ROW_ANCHORS = [
     ('canonicalise a row (v2_canon)', 'int v2_canon(u32 u'),
     ('prefix scan of row lengths (v2_scan, v2_seg)', 'struct V2Scan {'),
     ('n-gram keys, tf, list stores (v2_emit)', 'void v2_emit(const u16* ctok'),
-    ('df-table probe (v2_match4, v2_resolve)', 'int v2_match4(const u64'),
     ('video-table insert (v2_insert)', 'u32 v2_step(u32 h)'),
     ('video-table find (v2_find)', 'BOUNDED: the table came from'),
+]
+ANCHORS = [
+    ('df-table probe (v2_match4, v2_resolve)', 'int v2_match4(const u64'),
     ('process: slot decode, idf, tf-idf, store', 'void v2_process(const ScoreParams'),
     ('process: presence bits -> table (references)', 'if (EXCL) {'),
     ('process: bit walk (candidates)', 'const int idx = v2_find<T, BOUNDED>(tab, h, key);'),
@@ -42,12 +44,14 @@ ANCHORS = [
 def main():
     rep = sys.argv[1]
     videos = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
-    lines = open(SRC).read().splitlines()
-    starts = []
-    for name, anchor in ANCHORS:
-        idx = next(i for i, l in enumerate(lines) if anchor in l) + 1
-        starts.append((idx, name))
-    starts.sort()
+    by_file = {}
+    for fname, anchors in (('cst_score2.cuh', ANCHORS), ('cst_rows.cuh', ROW_ANCHORS)):
+        lines = open(os.path.join(CSRC, fname)).read().splitlines()
+        starts = []
+        for name, anchor in anchors:
+            idx = next(i for i, l in enumerate(lines) if anchor in l) + 1
+            starts.append((idx, name))
+        by_file[fname] = sorted(starts)
     raw = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--print-source', 'cuda,sass'],
                          capture_output=True, text=True).stdout
     cur, per = None, {}
@@ -63,9 +67,9 @@ def main():
     smp = sum(v[1] for v in per.values())
     acc = {}
     for (f, ln), v in per.items():
-        if f == 'cst_score2.cuh':
+        if f in by_file:
             cat = 'other'
-            for s0, name in starts:
+            for s0, name in by_file[f]:
                 if ln >= s0:
                     cat = name
         elif f == 'cst_common.cuh':
