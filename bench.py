@@ -493,6 +493,7 @@ def product_arm(args):
     del h_cand16, h_refs16
 
     # ---- the fused consumer of the reward (model.py:7-23): streaming kernels, HBM-bound ----
+    ok_other = True
     criterion = None
     if world == 1 and not args.no_criterion:
         # (timed through the C ABI: at 0.08 ms per launch the autograd wrapper's host time would be the number)
@@ -532,6 +533,34 @@ def product_arm(args):
                      'bound': 'hbm', 'bytes_per_token': 12,
                      'module_loss_equals_abi_loss': bool(float(loss) == float(out2[0]))}
         del seq, logp, loss, grad
+
+    # ---- the other reward scorers of train.py:119-124 on the same batch ---------
+    # BLEU-4 (k_bleu) and ROUGE-L (k_rouge), each followed by the SCB* baseline (k_scb), timed on the device;
+    # with the CPU leg on, the first videos' scores are held to the restated scorers as well.
+    other = None
+    if world == 1 and not args.no_other:
+        other = {}
+        n_o = min(64, n_videos)
+        for name, sc in (('bleu4', cst.Bleu(device=dev)), ('rouge_l', cst.Rouge(device=dev))):
+            for _ in range(3):
+                cst.get_cst_reward(d_cand, d_refs, sc, **kw)
+            ms_o = event_ms(lambda: cst.get_cst_reward(d_cand, d_refs, sc, **kw), args.steps, barrier)
+            other[name] = {'value': n_cap / (ms_o * 1e-3), 'unit': UNIT, 'ms_per_step': ms_o,
+                           'GBs': n_cap * BYTES_PER_CAPTION / ms_o / 1e6,
+                           'frac': n_cap * BYTES_PER_CAPTION / ms_o / 1e6 / peak,
+                           'kernels_per_step': 2}
+            if not args.no_cpu:
+                from oracle import bleu_rouge_oracle, reward_oracle
+                ref_sc = bleu_rouge_oracle.Bleu() if name == 'bleu4' else bleu_rouge_oracle.Rouge()
+                gts_o = [batch['refs'][v].astype(np.int64) for v in range(n_o)]
+                want = reward_oracle.score_rows(list(batch['sampled'][:n_o * SEQ_PER_IMG].astype(np.int64)), gts_o, ref_sc,
+                                                1, SEQ_PER_IMG, 1)
+                sub_o = cst.RefSet(d_refs.rows[:n_o * N_REFS], per_video=N_REFS)
+                got = sc.score_rows(d_cand[:n_o * SEQ_PER_IMG], sub_o, SEQ_PER_IMG, use_eos=1).cpu().numpy()
+                err = float(np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)))
+                other[name]['check'] = {'n_compared': int(want.size), 'max_rel_err': err,
+                                        'bit_exact': bool(np.array_equal(got, want)), 'ok': bool(err <= 1e-9)}
+                ok_other = ok_other and err <= 1e-9
 
     # ---- multi-GPU legs BASELINE.json lists beside the weak sweep (N > 1 only) --------------
     strong = None
@@ -656,12 +685,12 @@ def product_arm(args):
             'config': workload_config(n_videos, world), 'roofline': roofline, 'cpu_baseline': cpu, 'e2e': e2e,
             'gpu_launches': int(launches), 'clocks': clock_summary, 'int64_rows': int64_rows,
             'staged_refs': staged, 'e2e_staged': e2e_staged, 'criterion': criterion, 'strong': strong,
-            'config4': config4, 'check': check,
+            'config4': config4, 'other_scorers': other, 'check': check,
         }
         emit(line)
     if world > 1:
         dist.destroy_process_group()
-    if not ok:
+    if not ok or not ok_other:
         sys.stderr.write('bench.py: the GPU step does not match the CPU port on the sampled videos\n')
         return 1
     return 0
@@ -678,6 +707,7 @@ def main():
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-staged', action='store_true', help='skip the informational staged-references leg')
     ap.add_argument('--no-criterion', action='store_true', help='skip the RewardCriterion leg')
+    ap.add_argument('--no-other', action='store_true', help='skip the BLEU-4 / ROUGE-L scorer leg')
     ap.add_argument('--e2e-slices', type=int, default=16, help='video slices of the host pipeline')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -31,7 +31,6 @@
 #define MT_WARPS 8
 #define MT_THREADS (MT_WARPS * 32)
 #define MT_LIST_CAP 832
-#define MT_TAB_SLOTS 1193u            /* >= the instances of one candidate batch (MT_LIST_CAP), prime */
 #define MT_CTOK_U16 (CST2_ROWS * CST2_TOK_STRIDE + 8)
 #define RG_SLOTS 2048u                /* (token, reference) pairs of one batch of references: <= 1024 */
 #define RG_EMPTY 0xffffffffu
@@ -112,30 +111,35 @@ __device__ __forceinline__ void mt_video_refs(const RowsView& p, int64_t video, 
 // ---------------------------------------------------------------------------
 // BLEU
 // ---------------------------------------------------------------------------
-#define BL_OFF_LISTC ((size_t)MT_TAB_SLOTS * sizeof(VidSlot))
-#define BL_OFF_LISTR (BL_OFF_LISTC + (size_t)MT_LIST_CAP * sizeof(uint4))
-#define BL_OFF_CTOKC (BL_OFF_LISTR + (size_t)MT_LIST_CAP * sizeof(uint4))
-#define BL_OFF_CTOKR (BL_OFF_CTOKC + MT_CTOK_U16 * sizeof(u16))
-#define BL_SMEM (BL_OFF_CTOKR + MT_CTOK_U16 * sizeof(u16))
+// Shared memory, 37 KB so that six CTAs share an SM (at four the kernel waited on latency with half the
+// issue slots idle): the table, ONE list that candidates and references take turns in, the candidates'
+// instances boiled down to 4 bytes each (table slot, row, order, count) for the pass that follows the
+// references, one token buffer.
+#define BL_TAB_SLOTS 1103u            /* prime; holds the <= MT_LIST_CAP instances of one candidate batch */
+#define BL_OFF_LIST ((size_t)BL_TAB_SLOTS * sizeof(VidSlot))
+#define BL_OFF_CLIST (BL_OFF_LIST + (size_t)MT_LIST_CAP * sizeof(uint4))
+#define BL_OFF_CTOK (BL_OFF_CLIST + (size_t)MT_LIST_CAP * sizeof(u32))
+#define BL_SMEM (BL_OFF_CTOK + MT_CTOK_U16 * sizeof(u16))
+#define BL_NONE 0xffffffffu
 
 // bleu_out [4][n_total] (order-major: row 3 is the BLEU-4 vector the reward reads), comps_out [n_total][6]
 // = testlen, reflen, correct[4] (what the corpus-level score adds up; guess[k] = max(testlen - k, 0)).
-__global__ void __launch_bounds__(MT_THREADS, 4) k_bleu(const RowsView p, double* __restrict__ bleu_out,
+__global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double* __restrict__ bleu_out,
                                                         int* __restrict__ comps_out) {
-    constexpr u32 T = MT_TAB_SLOTS;
+    constexpr u32 T = BL_TAB_SLOTS;
     extern __shared__ __align__(16) unsigned char smem[];
-    __shared__ int sLc[CST2_ROWS], sLr[CST2_ROWS];
-    __shared__ int s_correct[CST2_ROWS][4];
+    __shared__ int sL[CST2_ROWS];
+    __shared__ int s_correct[CST2_ROWS][4];          // zero at kernel start, re-zeroed by its reader
     VidSlot* tab = reinterpret_cast<VidSlot*>(smem);
-    uint4* listC = reinterpret_cast<uint4*>(smem + BL_OFF_LISTC);
-    uint4* listR = reinterpret_cast<uint4*>(smem + BL_OFF_LISTR);
-    u16* ctokC = reinterpret_cast<u16*>(smem + BL_OFF_CTOKC);
-    u16* ctokR = reinterpret_cast<u16*>(smem + BL_OFF_CTOKR);
+    uint4* list = reinterpret_cast<uint4*>(smem + BL_OFF_LIST);
+    u32* clist = reinterpret_cast<u32*>(smem + BL_OFF_CLIST);
+    u16* ctok = reinterpret_cast<u16*>(smem + BL_OFF_CTOK);
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
     const int n_local = p.greedy ? 2 * S : S;
     const int64_t n_total = p.greedy ? 2 * p.n_cand : p.n_cand;
+    if (threadIdx.x < CST2_ROWS * 4) (&s_correct[0][0])[threadIdx.x] = 0;
 
 #pragma unroll 1
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
@@ -147,56 +151,67 @@ __global__ void __launch_bounds__(MT_THREADS, 4) k_bleu(const RowsView p, double
         bool first_batch = true;
 #pragma unroll 1
         for (int cb = 0; cb < n_local;) {
-            // ---- the candidate batch: rows -> instances -> table (counts start at 0) ----
+            // ---- the candidate batch: rows -> instances -> table (maxima start at 0) ----
             {
                 uint4* z = reinterpret_cast<uint4*>(tab);
 #pragma unroll 2
                 for (u32 i = threadIdx.x; i < T; i += MT_THREADS) z[i] = make_uint4(0, 0, 0, 0);
-                if (threadIdx.x < CST2_ROWS * 4) (&s_correct[0][0])[threadIdx.x] = 0;
             }
             const int n_try = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
-            mt_load_rows(cbase, gbase, S, cb, n_try, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
+            mt_load_rows(cbase, gbase, S, cb, n_try, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctok, sL, warp, lane);
             __syncthreads();
-            const V2Scan sc = v2_scan(sLc, n_try, MT_LIST_CAP, lane);
-            const int nC = sc.nfit;
-            if (warp == 0 && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
-            mt_emit_rows(ctokC, sc, listC, warp, lane);
+            int nC, n_entC, Lh;
+            {
+                const V2Scan sc = v2_scan(sL, n_try, MT_LIST_CAP, lane);
+                nC = sc.nfit;
+                n_entC = sc.n_ent;
+                Lh = sc.L;                           // lane h: testlen of candidate row h
+                if (warp == 0 && lane < nC) bad_rows += (u32)(sL[lane] >> 8);
+                mt_emit_rows(ctok, sc, list, warp, lane);
+            }
             __syncthreads();
 #pragma unroll 1
-            for (int i = (int)threadIdx.x; i < sc.n_ent; i += MT_THREADS) {
-                const uint4 e = listC[i];
-                if (e.z != 0u) {
+            for (int i = (int)threadIdx.x; i < n_entC; i += MT_THREADS) {
+                const uint4 e = list[i];
+                u32 c = BL_NONE;
+                if (e.z != 0u) {                     // first occurrence in its row: slot | row | order | count
                     const u64 key = (u64)e.x | ((u64)e.y << 32);
-                    listC[i].w = v2_insert<T>(tab, cst_hash(key), key);
+                    c = v2_insert<T>(tab, cst_hash(key), key) | ((e.z & 0x7fu) << 11) | ((e.z >> 8) << 18);
                 }
+                clist[i] = c;
             }
             // closest reference length of the lane's candidate (warp 0): (|l - testlen|, l) smallest
             u32 best = 0xffffffffu;
-            const int Lh = sc.L;                     // lane h: testlen of candidate row h
-            // ---- the references stream through ----
+            // ---- the references stream through (their loads start while other warps still insert: the
+            // token buffer is free once the candidates' instances are in the list) ----
 #pragma unroll 1
             for (int64_t rb = r0; rb < r1;) {
                 const int left = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
                 mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, left,
-                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
-                __syncthreads();                     // (also: every candidate key is in the table by now)
-                const V2Scan sr = v2_scan(sLr, left, MT_LIST_CAP, lane);
-                const int nR = sr.nfit;
-                if (warp == 0 && lane < nR && first_batch) bad_rows += (u32)(sLr[lane] >> 8);
-                mt_emit_rows(ctokR, sr, listR, warp, lane);
-                if (warp == 0) {
+                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctok, sL, warp, lane);
+                __syncthreads();                     // (also: every candidate key is in the table, the list is free,
+                                                     //  and the previous stage's finds are done with it)
+                int n_entR, nR;
+                {
+                    const V2Scan sr = v2_scan(sL, left, MT_LIST_CAP, lane);
+                    nR = sr.nfit;
+                    n_entR = sr.n_ent;
+                    if (warp == 0 && lane < nR && first_batch) bad_rows += (u32)(sL[lane] >> 8);
+                    mt_emit_rows(ctok, sr, list, warp, lane);
+                    if (warp == 0) {
 #pragma unroll 1
-                    for (int j = 0; j < nR; ++j) {
-                        const int l = __shfl_sync(CST_FULL, sr.L, j);
-                        const int d = (l > Lh) ? l - Lh : Lh - l;
-                        const u32 cand = ((u32)d << 8) | (u32)l;
-                        best = cand < best ? cand : best;
+                        for (int j = 0; j < nR; ++j) {
+                            const int l = __shfl_sync(CST_FULL, sr.L, j);
+                            const int d = (l > Lh) ? l - Lh : Lh - l;
+                            const u32 cand = ((u32)d << 8) | (u32)l;
+                            best = cand < best ? cand : best;
+                        }
                     }
                 }
                 __syncthreads();
 #pragma unroll 1
-                for (int i = (int)threadIdx.x; i < sr.n_ent; i += MT_THREADS) {
-                    const uint4 e = listR[i];
+                for (int i = (int)threadIdx.x; i < n_entR; i += MT_THREADS) {
+                    const uint4 e = list[i];
                     if (e.z != 0u) {
                         const u64 key = (u64)e.x | ((u64)e.y << 32);
                         const int idx = v2_find<T, false>(tab, cst_hash(key), key);
@@ -204,51 +219,58 @@ __global__ void __launch_bounds__(MT_THREADS, 4) k_bleu(const RowsView p, double
                     }
                 }
                 rb += nR;
-                __syncthreads();                     // listR, ctokR, sLr are reused; the maxima are final
             }
-            if (r0 >= r1) __syncthreads();           // (no references: the inserts still have to land)
+            __syncthreads();                         // the maxima are final (no references: the inserts have landed)
             // ---- clipped counts: min(count in the candidate, largest count in a reference) ----
 #pragma unroll 1
-            for (int i = (int)threadIdx.x; i < sc.n_ent; i += MT_THREADS) {
-                const uint4 e = listC[i];
-                if (e.z != 0u) {
-                    const u32 tf = e.z >> 8, mx = tab[e.w].P;
-                    const u32 c = tf < mx ? tf : mx;
-                    if (c) atomicAdd(&s_correct[e.z & 31u][(e.z >> 5) & 3u], (int)c);
+            for (int i = (int)threadIdx.x; i < n_entC; i += MT_THREADS) {
+                const u32 c = clist[i];
+                if (c != BL_NONE) {
+                    const u32 tf = c >> 18, mx = tab[c & 0x7ffu].P;
+                    const u32 m = tf < mx ? tf : mx;
+                    if (m) atomicAdd(&s_correct[(c >> 11) & 31u][(c >> 16) & 3u], (int)m);
                 }
             }
             __syncthreads();
-            // ---- BleuScorer.compute_score, the per-sentence part ----
-            if (warp == 0 && lane < nC) {
-                const int c = cb + lane;
-                const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
-                const int testlen = Lh;
-                const int reflen = (best == 0xffffffffu) ? 0 : (int)(best & 0xffu);
-                const double small = 1e-9, tiny = 1e-15;
-                const double ratio = ((double)testlen + tiny) / ((double)reflen + small);
-                const double bp = (ratio < 1.0) ? exp(1.0 - 1.0 / ratio) : 1.0;
-                double bleu = 1.0;
+            // ---- BleuScorer.compute_score, the per-sentence part (warp 0; the others go on to the next
+            // batch: nothing they touch before its first barrier is read here) ----
+            if (warp == 0) {
+                int cor[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const int guess = testlen > k ? testlen - k : 0;
-                    bleu *= ((double)s_correct[lane][k] + tiny) / ((double)guess + small);
-                    double b = (k == 0) ? bleu : (k == 1) ? sqrt(bleu) : pow(bleu, 1.0 / (double)(k + 1));
-                    if (ratio < 1.0) b *= bp;
-                    bleu_out[(size_t)k * (size_t)n_total + (size_t)out] = b;
+                    cor[k] = s_correct[lane][k];
+                    s_correct[lane][k] = 0;
                 }
-                if (comps_out) {
-                    int* q = comps_out + (size_t)out * 6;
-                    q[0] = testlen;
-                    q[1] = reflen;
-                    q[2] = s_correct[lane][0];
-                    q[3] = s_correct[lane][1];
-                    q[4] = s_correct[lane][2];
-                    q[5] = s_correct[lane][3];
+                if (lane < nC) {
+                    const int c = cb + lane;
+                    const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
+                    const int testlen = Lh;
+                    const int reflen = (best == 0xffffffffu) ? 0 : (int)(best & 0xffu);
+                    const double small = 1e-9, tiny = 1e-15;
+                    const double ratio = ((double)testlen + tiny) / ((double)reflen + small);
+                    const double bp = (ratio < 1.0) ? exp(1.0 - 1.0 / ratio) : 1.0;
+                    double bleu = 1.0;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int guess = testlen > k ? testlen - k : 0;
+                        bleu *= ((double)cor[k] + tiny) / ((double)guess + small);
+                        double b = (k == 0) ? bleu : (k == 1) ? sqrt(bleu) : pow(bleu, 1.0 / (double)(k + 1));
+                        if (ratio < 1.0) b *= bp;
+                        bleu_out[(size_t)k * (size_t)n_total + (size_t)out] = b;
+                    }
+                    if (comps_out) {
+                        int* q = comps_out + (size_t)out * 6;
+                        q[0] = testlen;
+                        q[1] = reflen;
+                        q[2] = cor[0];
+                        q[3] = cor[1];
+                        q[4] = cor[2];
+                        q[5] = cor[3];
+                    }
                 }
             }
             cb += nC;
             first_batch = false;
-            __syncthreads();
         }
         if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
     }
@@ -448,7 +470,7 @@ extern "C" int cst_bleu_scores(const void* cand, const void* greedy, int32_t can
         CST_CUDA_TRY(cudaFuncSetAttribute(k_bleu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BL_SMEM));
         if (device >= 0 && device < 64) attr_set[device] = true;     // (a constant: racing threads set the same value)
     }
-    k_bleu<<<mt_grid(device, n_videos, 4), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
+    k_bleu<<<mt_grid(device, n_videos, 6), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
     cst_count_launch();
     CST_CUDA_TRY(cudaGetLastError());
     return CST_OK;

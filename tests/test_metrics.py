@@ -363,7 +363,7 @@ def test_cuda_metric_scorers_refuse_what_they_cannot_do(gpu):
     with pytest.raises(ValueError):
         cst.Bleu(n=3, device=dev)
     rows = torch.zeros((2, 4, 8), dtype=torch.int32, device=dev)
-    table = cst.DfTable.from_rows(rows.reshape(8, 8), use_eos=1)
+    table = cst.DfTable.from_rows(rows, use_eos=1)
     cooked = cst.CookedRefs.cook(rows, cst.CiderD(df=table), use_eos=1)
     with pytest.raises(TypeError):
         cst.get_cst_reward(torch.zeros((8, 8), dtype=torch.int32, device=dev), cooked, cst.Rouge(device=dev),
