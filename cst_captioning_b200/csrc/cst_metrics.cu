@@ -32,8 +32,6 @@
 #define MT_THREADS (MT_WARPS * 32)
 #define MT_LIST_CAP 832
 #define MT_CTOK_U16 (CST2_ROWS * CST2_TOK_STRIDE + 8)
-#define RG_SLOTS 2048u                /* (token, reference) pairs of one batch of references: <= 1024 */
-#define RG_EMPTY 0xffffffffu
 
 struct RowsView {
     const void* cand;
@@ -279,26 +277,25 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double
 // ---------------------------------------------------------------------------
 // ROUGE-L
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ u32 rg_home(u32 key) { return (key * 0x9E3779B1u) >> 21; }   // 11 bits: RG_SLOTS
+// Per batch of references: a dictionary of their distinct tokens (open addressing, the slot is the
+// token's dense id) and a dense matrix mask[slot][reference] of position bits.  A candidate token is
+// looked up ONCE (-> its slot, or "in no reference"), not once per reference; the pair threads then
+// read their masks by index.  Capacity C = RG_MASK_WORDS / n slots for a batch of n references, and a
+// batch takes as many references as keep the dictionary at most 80 % full even if all tokens differ.
+#define RG_MASK_WORDS 6144            /* 24 KB */
+#define RG_DICT_MAX 1024u
+#define RG_NONE 0xffffffffu
 
-__device__ __forceinline__ u32 rg_find(const uint2* tab, u32 key) {
-    u32 idx = rg_home(key);
-#pragma unroll 1
-    for (;;) {
-        const uint2 s = tab[idx];
-        if (s.x == key) return s.y;
-        if (s.x == RG_EMPTY) return 0u;
-        idx = (idx + 1u) & (RG_SLOTS - 1u);
-    }
-}
+__device__ __forceinline__ u32 rg_home(u32 code, u32 C) { return __umulhi(code * 0x9E3779B1u, C); }
 
 __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, double* __restrict__ scores) {
-    __shared__ __align__(16) uint2 tab[RG_SLOTS];
+    __shared__ __align__(16) u32 mask[RG_MASK_WORDS];
+    __shared__ __align__(16) u32 dict[RG_DICT_MAX];
     __shared__ __align__(16) u16 ctokC[MT_CTOK_U16];
     __shared__ __align__(16) u16 ctokR[MT_CTOK_U16];
     __shared__ int sLc[CST2_ROWS], sLr[CST2_ROWS];
     __shared__ int s_lcs[CST2_ROWS];
-    __shared__ unsigned long long s_rec[CST2_ROWS];
+    __shared__ u32 s_key[CST2_ROWS];                 // best recall as floor(4096 lcs / len) | lcs | len
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
@@ -317,73 +314,124 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
             mt_load_rows(cbase, gbase, S, cb, nC, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
             if (threadIdx.x < CST2_ROWS) {
                 s_lcs[threadIdx.x] = 0;
-                s_rec[threadIdx.x] = 0ull;
+                s_key[threadIdx.x] = 0u;
             }
-            __syncthreads();
-            if (warp == 0 && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
+            bool cand_counted = false;
 #pragma unroll 1
-            for (int64_t rb = r0; rb < r1; rb += CST2_ROWS) {
-                const int nR = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
-#pragma unroll 2
-                for (u32 i = threadIdx.x; i < RG_SLOTS; i += MT_THREADS) tab[i] = make_uint2(RG_EMPTY, 0u);
-                mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, nR,
+            for (int64_t rb = r0; rb < r1;) {
+                const int left = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
+                {
+                    uint4* z = reinterpret_cast<uint4*>(mask);
+#pragma unroll
+                    for (int i = 0; i < RG_MASK_WORDS / 4 / MT_THREADS; ++i) z[threadIdx.x + i * MT_THREADS] = make_uint4(0, 0, 0, 0);
+                    uint4* d = reinterpret_cast<uint4*>(dict);
+                    d[threadIdx.x] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+                }
+                mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, left,
                              p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
                 __syncthreads();
+                // how many of the loaded references this batch takes (every warp works it out for itself)
+                int nR;
+                {
+                    const int L = (lane < left) ? (sLr[lane] & 0xff) : 0;
+                    int tok = (lane < left) ? (L > 0 ? L : 1) : 0;       // an empty sentence is ONE empty token
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int v = __shfl_up_sync(CST_FULL, tok, o);
+                        if (lane >= o) tok += v;
+                    }
+                    // tokens(n) <= 0.8 * min(RG_DICT_MAX, RG_MASK_WORDS / n)
+                    nR = __popc(__ballot_sync(CST_FULL, lane < left && (u32)tok * 5u <= 4u * RG_DICT_MAX &&
+                                                            (u32)tok * 5u * (u32)(lane + 1) <= 4u * RG_MASK_WORDS));
+                    if (nR < 1) nR = 1;                                  // (one row of 32 tokens always fits)
+                }
+                const u32 C = min((u32)RG_DICT_MAX, (u32)RG_MASK_WORDS / (u32)nR);
                 if (warp == 0 && cb == 0 && lane < nR) bad_rows += (u32)(sLr[lane] >> 8);
-                // positions of every token of every reference: mask of (token, reference).  An empty
-                // sentence is ONE empty token (split(" ")): code 0, which no word has.
+                if (warp == 1 && !cand_counted && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
+                cand_counted = true;
+                // ---- the references' tokens -> dictionary; position bit -> mask[slot][reference] ----
 #pragma unroll 1
                 for (int t = (int)threadIdx.x; t < nR * 32; t += MT_THREADS) {
                     const int r = t >> 5, j = t & 31;
                     const int L = sLr[r] & 0xff;
                     if (j < (L > 0 ? L : 1)) {
-                        const u32 key = (L > 0 ? (u32)ctokR[r * CST2_TOK_STRIDE + j] : 0u) | ((u32)r << 16);
-                        u32 idx = rg_home(key);
+                        const u32 code = L > 0 ? (u32)ctokR[r * CST2_TOK_STRIDE + j] : 0u;   // (0: the empty token)
+                        u32 idx = rg_home(code, C);
 #pragma unroll 1
                         for (;;) {
-                            const u32 cur = *reinterpret_cast<volatile u32*>(&tab[idx].x);
-                            if (cur == key) break;
-                            if (cur == RG_EMPTY) {
-                                const u32 old = atomicCAS(&tab[idx].x, RG_EMPTY, key);
-                                if (old == RG_EMPTY || old == key) break;
+                            const u32 cur = *reinterpret_cast<volatile u32*>(&dict[idx]);
+                            if (cur == code) break;
+                            if (cur == 0xffffffffu) {
+                                const u32 old = atomicCAS(&dict[idx], 0xffffffffu, code);
+                                if (old == 0xffffffffu || old == code) break;
                             }
-                            idx = (idx + 1u) & (RG_SLOTS - 1u);
+                            idx = (idx + 1u == C) ? 0u : idx + 1u;
                         }
-                        atomicOr(&tab[idx].y, 1u << j);
+                        atomicOr(&mask[idx * (u32)nR + (u32)r], 1u << j);
                     }
                 }
                 __syncthreads();
-                // a thread per (candidate, reference): my_lcs as the bit-vector recurrence
+                // ---- a warp per candidate: lane i looks token i up ONCE (-> its slot, or "in no reference of
+                // the batch"); then lane r runs my_lcs against reference r as the bit-vector recurrence, the
+                // slots going round by shuffle ----
 #pragma unroll 1
-                for (int t = (int)threadIdx.x; t < nC * nR; t += MT_THREADS) {
-                    const int h = t / nR, r = t - h * nR;
-                    const int Lh = sLc[h] & 0xff, Lr = sLr[r] & 0xff;
-                    const u32 rkey = (u32)r << 16;
-                    u32 V = 0xffffffffu;
-                    const u16* ct = ctokC + h * CST2_TOK_STRIDE;
+                for (int h = warp; h < nC; h += MT_WARPS) {
+                    const int Lh = sLc[h] & 0xff;
                     const int steps = Lh > 0 ? Lh : 1;
+                    u32 slot = RG_NONE;
+                    if (lane < steps) {
+                        const u32 code = Lh > 0 ? (u32)ctokC[h * CST2_TOK_STRIDE + lane] : 0u;
+                        u32 idx = rg_home(code, C);
+#pragma unroll 1
+                        for (;;) {
+                            const u32 cur = dict[idx];
+                            if (cur == code) { slot = idx; break; }
+                            if (cur == 0xffffffffu) break;
+                            idx = (idx + 1u == C) ? 0u : idx + 1u;
+                        }
+                    }
+                    const bool on = lane < nR;
+                    const u32* mr = mask + lane;
+                    u32 V = 0xffffffffu;
 #pragma unroll 1
                     for (int i = 0; i < steps; ++i) {
-                        const u32 M = rg_find(tab, (Lh > 0 ? (u32)ct[i] : 0u) | rkey);
-                        const u32 U = V & M;
-                        V = (V + U) | (V - U);
+                        const u32 d = __shfl_sync(CST_FULL, slot, i);
+                        if (d != RG_NONE) {          // (a token no reference of the batch holds leaves V as it is)
+                            const u32 U = on ? (V & mr[d * (u32)nR]) : 0u;
+                            V = (V + U) | (V - U);
+                        }
                     }
-                    const int lenr = Lr > 0 ? Lr : 1;
-                    const int lcs = __popc(~V & (lenr >= 32 ? 0xffffffffu : ((1u << lenr) - 1u)));
-                    atomicMax(&s_lcs[h], lcs);                                   // prec = lcs / len(candidate)
-                    const double rec = (double)lcs / (double)lenr;               // rec  = lcs / len(reference)
-                    atomicMax(&s_rec[h], (unsigned long long)__double_as_longlong(rec));   // (>= 0: bit order = value order)
+                    // prec = lcs / len(candidate): the largest lcs; rec = lcs / len(reference): fractions with
+                    // denominators <= 32 differ by >= 2^-10, so floor(4096 lcs / len) orders them, and equal
+                    // fractions are equal doubles whichever (lcs, len) pair speaks for them
+                    u32 lcs = 0u, key = 0u;
+                    if (on) {
+                        const int Lr = sLr[lane] & 0xff;
+                        const u32 lenr = (u32)(Lr > 0 ? Lr : 1);
+                        lcs = (u32)__popc(~V & (lenr >= 32u ? 0xffffffffu : ((1u << lenr) - 1u)));
+                        key = (((lcs << 12) / lenr) << 12) | (lcs << 6) | lenr;
+                    }
+                    lcs = __reduce_max_sync(CST_FULL, lcs);
+                    key = __reduce_max_sync(CST_FULL, key);
+                    if (lane == 0) {                 // (one warp owns a candidate: no atomics)
+                        if ((int)lcs > s_lcs[h]) s_lcs[h] = (int)lcs;
+                        if (key > s_key[h]) s_key[h] = key;
+                    }
                 }
+                rb += nR;
                 __syncthreads();
             }
+            if (r0 >= r1) __syncthreads();
             // Rouge.calc_score: F-measure of the two maxima, in the scorer's operation order
             if (threadIdx.x < nC) {
                 const int h = (int)threadIdx.x;
                 const int c = cb + h;
                 const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
                 const int Lh = sLc[h] & 0xff;
+                if (r0 >= r1) bad_rows += (u32)(sLc[h] >> 8);
                 const double prec = (double)s_lcs[h] / (double)(Lh > 0 ? Lh : 1);
-                const double rec = __longlong_as_double((long long)s_rec[h]);
+                const u32 kbest = s_key[h];
+                const double rec = kbest ? (double)((kbest >> 6) & 63u) / (double)(kbest & 63u) : 0.0;
                 const double beta2 = 1.2 * 1.2;
                 double score = 0.0;
                 if (prec != 0.0 && rec != 0.0)
