@@ -6,4 +6,4 @@ set -e
 name=$1; shift
 cd "$(dirname "$0")/../cst_captioning_b200/csrc"
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -shared \
-     -I../../include "$@" -o ../libcst_var_$name.so cst_reward.cu cst_criterion.cu
+     -I../../include "$@" -o ../libcst_var_$name.so *.cu
