@@ -85,21 +85,22 @@ class Bleu(_RowScorer):
         super().__init__(device)
         self._n = n
 
-    def bleu_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, comps=False):
+    def bleu_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, comps=False, bad=None):
         """-> float64 CUDA tensor (4, n_total) of sentence BLEU-1..4 (and, with ``comps``, the int32
-        (n_total, 6) statistics testlen, reflen, correct[4])."""
+        (n_total, 6) statistics testlen, reflen, correct[4]).  ``bad``: int32 CUDA tensor (1,) that the
+        number of rows holding ids outside [-1, 65534] is added to."""
         dev = self.device
         n_total = cand.shape[0] * (2 if greedy is not None else 1)
         out = torch.empty((4, n_total), dtype=torch.float64, device=dev)
         stats = torch.empty((n_total, 6), dtype=torch.int32, device=dev) if comps else None
         check(lib.cst_bleu_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos), out.data_ptr(),
-                                  stats.data_ptr() if comps else None, None, dev.index,
+                                  stats.data_ptr() if comps else None, bad.data_ptr() if bad is not None else None, dev.index,
                                   torch.cuda.current_stream(dev).cuda_stream))
         return (out, stats) if comps else out
 
-    def score_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None):
+    def score_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, bad=None):
         """BLEU-4 of token rows -> float64 CUDA tensor (n_total,): what the reward reads."""
-        return self.bleu_rows(cand, refs, cands_per_video, use_eos, greedy)[3]
+        return self.bleu_rows(cand, refs, cands_per_video, use_eos, greedy, bad=bad)[3]
 
     def compute_score(self, gts, res):
         """-> ([BLEU-1..4 of the corpus], [4 lists of sentence scores])."""
@@ -129,10 +130,12 @@ class Rouge(_RowScorer):
         super().__init__(device)
         self.beta = 1.2
 
-    def score_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None):
+    def score_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, bad=None):
+        """ROUGE-L of token rows -> float64 CUDA tensor (n_total,); ``bad`` as in ``Bleu.bleu_rows``."""
         dev = self.device
         out = torch.empty(cand.shape[0] * (2 if greedy is not None else 1), dtype=torch.float64, device=dev)
-        check(lib.cst_rouge_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos), out.data_ptr(), None,
+        check(lib.cst_rouge_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos), out.data_ptr(),
+                                   bad.data_ptr() if bad is not None else None,
                                    dev.index, torch.cuda.current_stream(dev).cuda_stream))
         return out
 

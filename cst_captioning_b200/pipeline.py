@@ -14,7 +14,7 @@ from __future__ import annotations
 import torch
 
 from . import _lib
-from .reward import CookedRefs, RefSet, get_cst_reward
+from .reward import CookedRefs, RefSet, _scorer_device, get_cst_reward
 
 
 class HostRewardPipeline:
@@ -30,7 +30,7 @@ class HostRewardPipeline:
     def __init__(self, scorer, seq_per_img=20, scb_captions=20, scb_baseline=1, use_eos=0, use_mixer=1,
                  slices=16):
         self.scorer = scorer
-        self.device = scorer.table.device
+        self.device = _scorer_device(scorer)             # CiderD, or the Bleu / Rouge scorers
         self.kw = dict(expand_feat=1, seq_per_img=seq_per_img, scb_captions=scb_captions,
                        scb_baseline=scb_baseline, use_eos=use_eos, use_mixer=use_mixer, return_stats=True)
         self.seq_per_img = seq_per_img

@@ -349,13 +349,15 @@ def _reward_from_scores(scorer, sampled, greedy, refs, cands_per_video, use_eos,
     if n % seq_per_img:
         raise ValueError('cannot reshape %d scores into rows of %d' % (n, seq_per_img))
     stats = torch.empty(_lib.N_STATS, dtype=torch.float64, device=dev)
-    scores = scorer.score_rows(sampled, refs, cands_per_video, use_eos, greedy=greedy)
+    bad = torch.zeros(1, dtype=torch.int32, device=dev)
+    scores = scorer.score_rows(sampled, refs, cands_per_video, use_eos, greedy=greedy, bad=bad)
     other = scores[n:] if greedy is not None else bcmr
     stream = _stream(dev)
     scratch = _scratch_for(dev, n // seq_per_img, stream)
     check(lib.cst_scb_apply(scores.data_ptr(), other.data_ptr() if other is not None else None, n // seq_per_img,
                             seq_per_img, mode, k, reward.data_ptr(), stats.data_ptr(), scratch.data_ptr(),
                             scratch.numel(), dev.index, stream))
+    stats[4:5] = bad                                    # rows with ids outside [-1, 65534], as cst_reward counts them
     return reward, stats
 
 

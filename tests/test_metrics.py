@@ -371,7 +371,32 @@ def test_cuda_metric_scorers_refuse_what_they_cannot_do(gpu):
     with pytest.raises(TypeError):
         cst.get_cst_reward(torch.zeros((8, 8), dtype=torch.int32, device=dev), rows, object(), expand_feat=1,
                            seq_per_img=4)
+    # ids outside [0, 65534] end the caption and are counted, like in cst_reward (stats[4])
+    cand = torch.tensor([[5, 6, 70000, 7], [5, 6, 0, 0]], dtype=torch.int64, device=dev)
+    refs2 = torch.tensor([[[5, 6, 0, 0]]], dtype=torch.int64, device=dev)
+    for sc in (cst.Bleu(device=dev), cst.Rouge(device=dev)):
+        rew, m, b, st = cst.get_cst_reward(cand, refs2, sc, expand_feat=1, seq_per_img=2, scb_captions=0,
+                                           return_stats=True)
+        assert float(st[4]) == 1.0 and float(rew[0, 0]) == float(rew[1, 0])
     # an empty shard is nothing to score
     rew, m, b = cst.get_cst_reward(torch.zeros((0, 8), dtype=torch.int32, device=dev), rows[:0], cst.Bleu(device=dev),
                                    expand_feat=1, seq_per_img=4, scb_captions=0)
     assert rew.shape == (0, 8)
+
+
+@pytest.mark.gpu
+def test_cuda_host_pipeline_takes_these_scorers(gpu):
+    """Pinned host rows through HostRewardPipeline (upload overlapped with scoring) = one launch on device rows."""
+    cst, torch, dev = gpu
+    from cst_captioning_b200 import synth
+    b = synth.make_batch(300, 20, 20, seed=77)
+    h_c, h_r = torch.from_numpy(b['sampled']).pin_memory(), torch.from_numpy(b['refs']).pin_memory()
+    for sc in (cst.Bleu(device=dev), cst.Rouge(device=dev)):
+        want, wm, wb = cst.get_cst_reward(h_c.to(dev), h_r.to(dev), sc, expand_feat=1, seq_per_img=20, scb_captions=5,
+                                          scb_baseline=2, use_eos=1)
+        pipe = cst.HostRewardPipeline(sc, seq_per_img=20, scb_captions=5, scb_baseline=2, use_eos=1, slices=7)
+        out, stats = pipe(h_c, h_r)
+        torch.cuda.synchronize()
+        np.testing.assert_array_equal(out.numpy(), want[:, 0].cpu().numpy())
+        assert float(stats[5]) == pytest.approx(float(wm), rel=1e-12)
+        assert float(stats[6]) == pytest.approx(float(wb), rel=1e-12)
