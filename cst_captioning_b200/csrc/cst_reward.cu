@@ -585,22 +585,49 @@ struct ScoreParams {
 
 #include "cst_score2.cuh"
 
-// Standalone baseline over (n_groups, S) scores: one warp per group.
+// Standalone baseline over (n_groups, S) scores: one warp per group.  Groups of up to 32 scores (every
+// training shape) stay in registers, lane = caption: ranks by shuffle, no second pass over memory.
+// fold_apart: the statistics are folded by k_fold_stats after the launch (large batches).
 __global__ void __launch_bounds__(128) k_scb(const double* __restrict__ scores, const double* __restrict__ other,
                                              int64_t n_groups, int S, int mode, int k, float* reward,
-                                             double* stats, u32* ctl, double* partials, double n_m, double n_b) {
+                                             double* stats, u32* ctl, double* partials, double n_m, double n_b,
+                                             int fold_apart) {
     extern __shared__ __align__(16) unsigned char smem[];
     double* red = reinterpret_cast<double*>(smem);   // [8]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int64_t g = (int64_t)blockIdx.x * 4 + warp; g < n_groups; g += (int64_t)gridDim.x * 4) {
         double sm, sb;
-        baseline_group(scores + g * S, other ? other + g * S : nullptr, S, mode, k, lane, reward + g * S, sm, sb);
+        if (S <= 32) {
+            const bool on = lane < S;
+            const double s = on ? scores[g * S + lane] : 0.0;
+            const double o = (on && other) ? other[g * S + lane] : 0.0;
+            const bool scb = (mode == CST_BASE_SCB_GT || mode == CST_BASE_SCB_SAMPLE);
+            const double x = (mode == CST_BASE_SCB_GT) ? o : s;
+            double low = 0.0;
+            if (scb) {
+                int rank = 0;
+                if (k < S) {                         // k lowest (utils.py:294-312): ties by index = stable sort
+#pragma unroll 1
+                    for (int j = 0; j < S; ++j) {
+                        const double xj = __shfl_sync(CST_FULL, x, j);
+                        rank += (xj < x || (xj == x && j < lane)) ? 1 : 0;
+                    }
+                }
+                low = warp_sum((on && rank < k) ? x : 0.0);
+            }
+            const double base = scb ? low / (double)k : 0.0;
+            if (on) reward[g * S + lane] = (float)((mode == CST_BASE_GREEDY) ? s - o : s - base);
+            sm = warp_sum(s);
+            sb = (mode == CST_BASE_SCB_SAMPLE) ? low : (mode == CST_BASE_NONE) ? 0.0 : warp_sum(o);
+        } else {
+            baseline_group(scores + g * S, other ? other + g * S : nullptr, S, mode, k, lane, reward + g * S, sm, sb);
+        }
         if (lane == 0) {
             partials[2 * g] = sm;
             partials[2 * g + 1] = sb;
         }
     }
-    fold_stats_if_last(ctl, partials, n_groups, n_m, n_b, stats, red);
+    if (!fold_apart) fold_stats_if_last(ctl, partials, n_groups, n_m, n_b, stats, red);
 }
 
 // ---------------------------------------------------------------------------
@@ -852,11 +879,19 @@ extern "C" int cst_scb_apply(const double* scores, const double* other, int64_t 
     const size_t smem = 8 * sizeof(double);
     int64_t blocks = (n_rows + 3) / 4;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    k_scb<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(
-        scores, other, n_rows, seq_per_img, mode, scb_k, reward_out, stats_out, reinterpret_cast<u32*>(scratch),
-        reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256), n_m, n_b);
+    // a 128-thread CTA folding tens of thousands of partials is most of such a launch: large batches fold apart
+    const int fold_apart = n_rows >= 4096;
+    u32* ctl = reinterpret_cast<u32*>(scratch);
+    double* partials = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256);
+    k_scb<<<(unsigned)blocks, 128, smem, (cudaStream_t)stream>>>(scores, other, n_rows, seq_per_img, mode, scb_k,
+                                                               reward_out, stats_out, ctl, partials, n_m, n_b, fold_apart);
     COUNT_LAUNCH();
     CUDA_TRY(cudaGetLastError());
+    if (fold_apart) {
+        k_fold_stats<<<1, 1024, 2 * 32 * sizeof(double), (cudaStream_t)stream>>>(ctl, partials, n_rows, n_m, n_b, stats_out);
+        COUNT_LAUNCH();
+        CUDA_TRY(cudaGetLastError());
+    }
     return CST_OK;
 }
 
