@@ -7,7 +7,7 @@ Public surface (mirrors the reference's interfaces for this path):
                                        raw caption words or id strings)
 * :class:`Bleu`, :class:`Rouge`        <- ``pycocoevalcap`` ``Bleu`` / ``Rouge``: the other reward scorers of
                                        ``train.py:119-124`` (``--eval_metric Bleu_4`` / ``ROUGE_L``)
-* :func:`language_eval`                <- the CIDEr entry of ``utils.language_eval`` (``utils.py:114-132``)
+* :func:`language_eval`                <- ``utils.language_eval`` (``utils.py:114-132``): Bleu_1..4, ROUGE_L, CIDEr
 * :func:`get_cst_reward`               <- ``utils.get_cst_reward`` (``utils.py:229``)
 * :func:`get_self_critical_reward`     <- ``utils.get_self_critical_reward`` (``utils.py:169``)
 * :class:`DfTable`                     <- the ``*_ciderdf.pkl`` of ``compute_ciderdf.py``

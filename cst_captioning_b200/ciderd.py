@@ -268,12 +268,14 @@ def _tokenize(caption):
 
 
 def language_eval(gold_file, pred_file, device=None, on_long='truncate'):
-    """The CIDEr entry of ``utils.language_eval`` (``utils.py:114-132``), which ``train.py:35-42,
-    353-358`` calls on the validation predictions and ``check_model`` (``train.py:386-391``)
-    reads as ``infos['CIDEr']``: corpus-mode CIDEr of ``pred_file``'s captions against the
-    references of ``gold_file`` (both cocofmt json), on the device.  -> {'CIDEr': score}.
-    BLEU / METEOR / ROUGE_L are not computed here (Java tools; out of this path)."""
+    """``utils.language_eval`` (``utils.py:114-132``), which ``train.py:35-42, 353-358`` calls on the
+    validation predictions and ``check_model`` (``train.py:386-391``) reads through ``opt.eval_metric``:
+    the corpus scores COCOEvalCap reports for ``pred_file``'s captions against the references of
+    ``gold_file`` (both cocofmt json), on the device -> {'Bleu_1' .. 'Bleu_4', 'ROUGE_L', 'CIDEr'}, rounded
+    to 5 places like the reference.  METEOR is a Java program and is not computed; the PTB tokenizer (Java
+    as well) is replaced by lower-casing and its punctuation list."""
     import json
+    from .metrics import Bleu, Rouge
     gts = load_gt_refs(gold_file)
     with open(pred_file) as fh:
         preds = json.load(fh)
@@ -281,5 +283,12 @@ def language_eval(gold_file, pred_file, device=None, on_long='truncate'):
         preds = preds.get('predictions', preds)
     res = {p['image_id']: [_tokenize(p['caption'])] for p in preds}
     gts = {k: [_tokenize(c) for c in gts[k]] for k in res}
+    out = {}
+    bleus, _ = Bleu(device=device, on_long=on_long).compute_score(gts, res)
+    for k, b in enumerate(bleus):
+        out['Bleu_%d' % (k + 1)] = round(float(b), 5)
+    rouge, _ = Rouge(device=device, on_long=on_long).compute_score(gts, res)
+    out['ROUGE_L'] = round(float(rouge), 5)
     score, _ = Cider(device=device, on_long=on_long).compute_score(gts, res)
-    return {'CIDEr': round(float(score), 5)}
+    out['CIDEr'] = round(float(score), 5)
+    return out

@@ -45,8 +45,10 @@ def _row_args(cand, greedy, refs, cands_per_video, use_eos):
 class _RowScorer:
     """What the reward functions need of a scorer that is not ``CiderD``."""
 
-    def __init__(self, device=None):
+    def __init__(self, device=None, on_long='error'):
         self.device = _device(device)
+        self._on_long = on_long          # captions beyond the 32 tokens of a kernel row: 'error' or 'truncate'
+        self.truncated = 0
 
     def _strings_to_rows(self, gts, res, sep):
         """dict protocol -> (candidate rows, RefSet, cands per video): every distinct word of the call is
@@ -55,7 +57,7 @@ class _RowScorer:
         assert gts.keys() == res.keys()
         keys = list(gts.keys())
         width = _lib.MAX_ROW_WIDTH
-        words = WordIds(max_tokens=width)
+        words = WordIds(max_tokens=width, on_long=self._on_long)
         cand = np.full((len(keys), width), -1, dtype=np.int32)
         counts, ref_rows = [], []
         for i, key in enumerate(keys):
@@ -67,6 +69,7 @@ class _RowScorer:
             counts.append(len(refs))
             for r in refs:
                 ref_rows.append(_row(words.ids(r, sep=sep), width))
+        self.truncated += words.truncated
         dev = self.device
         rows = torch.from_numpy(np.stack(ref_rows)).to(dev)
         if len(set(counts)) == 1:
@@ -79,10 +82,10 @@ class _RowScorer:
 class Bleu(_RowScorer):
     """Sentence and corpus BLEU-1..4, ``BleuScorer.compute_score(option='closest')``."""
 
-    def __init__(self, n=4, device=None):
+    def __init__(self, n=4, device=None, on_long='error'):
         if n != 4:
             raise ValueError('the sm_100a kernel implements n=4 (the reference default)')
-        super().__init__(device)
+        super().__init__(device, on_long)
         self._n = n
 
     def bleu_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, comps=False, bad=None):
@@ -126,8 +129,8 @@ class Bleu(_RowScorer):
 class Rouge(_RowScorer):
     """ROUGE-L F-measure (beta = 1.2) of ``Rouge.calc_score``."""
 
-    def __init__(self, device=None):
-        super().__init__(device)
+    def __init__(self, device=None, on_long='error'):
+        super().__init__(device, on_long)
         self.beta = 1.2
 
     def score_rows(self, cand, refs, cands_per_video, use_eos=0, greedy=None, bad=None):

@@ -111,5 +111,13 @@ def test_long_captions_and_language_eval(tmp_path):
     (tmp_path / 'gold.json').write_text(json.dumps(gold))
     (tmp_path / 'pred.json').write_text(json.dumps(preds))
     out = cst.language_eval(str(tmp_path / 'gold.json'), str(tmp_path / 'pred.json'))
-    score, _ = co.Cider().compute_score({k: refs[k] for k in ids}, {k: [refs[k][0] + ' the'] for k in ids})
-    assert out == {'CIDEr': round(float(score), 5)}
+    g2, r2 = {k: refs[k] for k in ids}, {k: [refs[k][0] + ' the'] for k in ids}
+    score, _ = co.Cider().compute_score(g2, r2)
+    assert out['CIDEr'] == round(float(score), 5)
+    # ... and the other corpus scores COCOEvalCap reports (Bleu_1..4, ROUGE_L; METEOR is a Java tool)
+    from oracle import bleu_rouge_oracle as bo
+    bleus, _ = bo.Bleu().compute_score(g2, r2)
+    rouge, _ = bo.Rouge().compute_score(g2, r2)
+    want = {'Bleu_%d' % (k + 1): round(float(b), 5) for k, b in enumerate(bleus)}
+    want.update({'ROUGE_L': round(float(rouge), 5), 'CIDEr': round(float(score), 5)})
+    assert out == want
