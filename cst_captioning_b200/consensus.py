@@ -1,4 +1,4 @@
-"""GT consensus scores on the device: the CIDEr column of ``compute_scores.py``.
+"""GT consensus scores on the device: the CIDEr, Bleu_4 and ROUGE_L columns of ``compute_scores.py``.
 
 ``compute_scores.py:75-103`` (``make compute_evalscores``, run with
 ``--remove_in_ref``, ``Makefile:118-120``) scores caption i of every video against the
@@ -17,6 +17,11 @@ scoring column i against the rest with the same fused kernel as the RL path.  Vi
 exceed one shared-memory table (more than 32 captions or 1,100 n-gram instances) fall back to one
 device-built table per pass.
 
+The ``Bleu_4`` and ``ROUGE_L`` columns (``compute_scores.py:67-68``; ``METEOR`` is a Java program) need
+no corpus statistics: pass i is one launch of ``k_bleu`` / ``k_rouge`` on caption i against the others.
+``evalscores`` computes the columns wanted and ``write_evalscores_pkl`` stores them the way
+``compute_scores.py:105-108`` does, for ``dataloader.py:66-73`` to read (``--eval_metric`` picks the key).
+
 Difference in input, not in arithmetic: the reference scores the raw caption *words*
 of the cocofmt json, this module scores token-id rows.  They agree when the rows hold
 every word of the caption (a vocabulary without ``<unk>`` folding, captions of at most
@@ -32,10 +37,13 @@ from .df_table import DfTable, _row_dtype
 from .reward import RefSet
 
 
-def consensus_scores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0):
+def consensus_scores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0, metric='CIDEr'):
     """``refs``: CUDA int tensor ``(videos, R, W)`` of reference rows (``[<start>, w..,
     <end>, pad]`` label rows or bare word rows).  -> float64 CUDA tensor
-    ``(videos, seq_per_img)``: column i = CIDEr-D of caption i against the others."""
+    ``(videos, seq_per_img)``: column i = score of caption i against the others under ``metric``
+    ('CIDEr', 'Bleu_4' or 'ROUGE_L': the keys of ``compute_scores.py:67-68``)."""
+    if metric not in ('CIDEr', 'Bleu_4', 'ROUGE_L'):
+        raise ValueError("metric must be 'CIDEr', 'Bleu_4' or 'ROUGE_L' (METEOR is a Java program)")
     if not (torch.is_tensor(refs) and refs.is_cuda and refs.dim() == 3):
         raise ValueError('refs must be a CUDA tensor (videos, refs, width)')
     n_videos, n_refs, width = refs.shape
@@ -48,6 +56,17 @@ def consensus_scores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0):
     dev = refs.device
     out = torch.empty(n_videos, seq_per_img, dtype=torch.float64, device=dev)
     if n_videos == 0:
+        return out
+    if metric != 'CIDEr':
+        from .metrics import Bleu, Rouge
+        scorer = Bleu(device=dev) if metric == 'Bleu_4' else Rouge(device=dev)
+        for i in range(seq_per_img):                          # compute_scores.py:81-92, no corpus statistics
+            if remove_in_ref:
+                others = torch.cat([refs[:, :i], refs[:, i + 1:]], dim=1).contiguous()
+            else:
+                others = refs
+            refset = RefSet(others.reshape(-1, width), per_video=others.shape[1])
+            out[:, i] = scorer.score_rows(refs[:, i].contiguous(), refset, 1, use_eos=use_eos)
         return out
     table = DfTable.from_rows(refs, use_eos=use_eos)          # df of ALL captions, ref_len = log(videos)
     scorer = CiderD(df=table)
@@ -83,3 +102,18 @@ def consensus_scores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0):
     torch.cuda.current_stream(dev).synchronize()              # the table is freed with `scorer`
     table.close()
     return out
+
+
+def evalscores(refs, seq_per_img=None, remove_in_ref=True, use_eos=0, metrics=('Bleu_4', 'ROUGE_L', 'CIDEr')):
+    """The table ``compute_scores.py:75-103`` builds: {metric: float64 CUDA tensor (videos, seq_per_img)}."""
+    return {m: consensus_scores(refs, seq_per_img, remove_in_ref, use_eos, metric=m) for m in metrics}
+
+
+def write_evalscores_pkl(path, scores):
+    """``compute_scores.py:105-108``: the dict of (videos, seq_per_img) float64 arrays, pickled with the
+    highest protocol -- what ``dataloader.py:66-73`` loads as ``bcmrscores_pkl``."""
+    import pickle
+    host = {m: (v.cpu().numpy() if torch.is_tensor(v) else v) for m, v in scores.items()}
+    with open(path, 'wb') as fh:
+        pickle.dump(host, fh, protocol=pickle.HIGHEST_PROTOCOL)
+    return host

@@ -400,3 +400,30 @@ def test_cuda_host_pipeline_takes_these_scorers(gpu):
         np.testing.assert_array_equal(out.numpy(), want[:, 0].cpu().numpy())
         assert float(stats[5]) == pytest.approx(float(wm), rel=1e-12)
         assert float(stats[6]) == pytest.approx(float(wb), rel=1e-12)
+
+
+@pytest.mark.gpu
+def test_cuda_consensus_columns_bleu_rouge(gpu, tmp_path):
+    """The Bleu_4 and ROUGE_L columns of compute_scores.py:75-103 (caption i against the others) and the
+    pickle the data loader reads them from."""
+    import pickle
+    cst, torch, dev = gpu
+    from cst_captioning_b200 import consensus, synth
+    rng = np.random.default_rng(31)
+    corpus, _ = synth.make_refs(rng, 60, 7, vocab=50)
+    refs = torch.from_numpy(corpus).to(dev)
+    got = consensus.evalscores(refs)
+    assert set(got) == {'Bleu_4', 'ROUGE_L', 'CIDEr'}
+    strings = [[ro.row_to_str(corpus[v, r], 0) for r in range(7)] for v in range(60)]
+    for i in range(7):
+        preds = {v: [strings[v][i]] for v in range(60)}
+        gts = {v: strings[v][:i] + strings[v][i + 1:] for v in range(60)}
+        _, lists = bo.Bleu().compute_score(gts, preds)
+        np.testing.assert_allclose(got['Bleu_4'][:, i].cpu().numpy(), np.array(lists[-1]), rtol=1e-12, atol=1e-300)
+        _, want = bo.Rouge().compute_score(gts, preds)
+        np.testing.assert_array_equal(got['ROUGE_L'][:, i].cpu().numpy(), want)
+    host = consensus.write_evalscores_pkl(str(tmp_path / 'evalscores.pkl'), got)
+    back = pickle.load(open(tmp_path / 'evalscores.pkl', 'rb'))
+    assert set(back) == set(host) and back['ROUGE_L'].shape == (60, 7) and back['CIDEr'].dtype == np.float64
+    with pytest.raises(ValueError):
+        consensus.consensus_scores(refs, metric='METEOR')
