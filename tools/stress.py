@@ -1,4 +1,4 @@
-"""Stress k_score2 over many random shapes (ragged lengths, long rows, more references than one table
+"""Stress k_score2 (and k_bleu / k_rouge) over many random shapes (ragged lengths, long rows, more references than one table
 takes, candidate counts beyond one batch): repeated launches must agree bit for bit (determinism),
 the fused launch must agree with a per-candidate rescoring, and staged references with raw rows.
 Run under `timeout`: a hang would show as a timeout, not as a wrong number."""
@@ -16,6 +16,7 @@ rng = np.random.default_rng(99)
 corpus, _ = synth.make_refs(rng, 500, 20, vocab=300)
 scorer = cst.CiderD(df=cst.DfTable.from_rows(torch.from_numpy(corpus).to(dev), use_eos=1))
 n_cases = int(sys.argv[1]) if len(sys.argv) > 1 else 150
+metric_scorers = [cst.Bleu(device=dev), cst.Rouge(device=dev)]
 t0 = time.time()
 for case in range(n_cases):
     n_videos = int(rng.integers(1, 3000))
@@ -68,5 +69,15 @@ for case in range(n_cases):
         del cooked
     g2 = torch.roll(c, 1, 0)
     cst.get_self_critical_reward(c, g2, r, scorer, expand_feat=1, seq_per_img=s, use_eos=ue)
+    # the BLEU-4 / ROUGE-L kernels: repeated launches agree bit for bit, and the batched launch (candidate
+    # batches, reference stages) gives the scores of one candidate per "video" (a single short stage each)
+    rs = RefSet.coerce(r, dev)
+    for sc in metric_scorers:
+        a1 = sc.score_rows(c, rs, s, use_eos=ue, greedy=g2)
+        a2 = sc.score_rows(c, rs, s, use_eos=ue, greedy=g2)
+        assert torch.equal(a1, a2), '%s: non-deterministic result in case %d' % (type(sc).__name__, case)
+        b1 = sc.score_rows(c[:per.n_videos], per, 1, use_eos=ue)
+        assert torch.equal(a1[:per.n_videos], b1), '%s: batched vs per-candidate mismatch in case %d' % (type(sc).__name__, case)
+        assert bool(torch.isfinite(a1).all()) and float(a1.min()) >= 0.0 and float(a1.max()) <= 1.0 + 1e-9
 torch.cuda.synchronize()
 print('stress ok: %d cases in %.1f s' % (n_cases, time.time() - t0))
