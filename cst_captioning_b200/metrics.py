@@ -29,8 +29,10 @@ def _device(device):
     return dev
 
 
-def _row_args(cand, greedy, refs, cands_per_video, use_eos):
+def _row_args(cand, greedy, refs, cands_per_video, use_eos, dev):
     n = cand.shape[0]
+    if cand.device != dev or refs.rows.device != dev or (greedy is not None and greedy.device != dev):
+        raise ValueError('rows must live on the scorer\'s device %s' % dev)
     if greedy is not None and (greedy.shape != cand.shape or greedy.dtype != cand.dtype or
                                greedy.stride(0) != cand.stride(0)):
         raise ValueError('greedy rows must share the geometry of the sampled rows')
@@ -51,8 +53,8 @@ class _RowScorer:
         self.truncated = 0
 
     def _strings_to_rows(self, gts, res, sep):
-        """dict protocol -> (candidate rows, RefSet, cands per video): every distinct word of the call is
-        interned to an id; consecutive entries that share one reference list share a video."""
+        """dict protocol -> (candidate rows, RefSet): every distinct word of the call is interned to an
+        id; each entry is a "video" of its own (one candidate against its list of references)."""
         from .reward import RefSet
         assert gts.keys() == res.keys()
         keys = list(gts.keys())
@@ -96,7 +98,7 @@ class Bleu(_RowScorer):
         n_total = cand.shape[0] * (2 if greedy is not None else 1)
         out = torch.empty((4, n_total), dtype=torch.float64, device=dev)
         stats = torch.empty((n_total, 6), dtype=torch.int32, device=dev) if comps else None
-        check(lib.cst_bleu_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos), out.data_ptr(),
+        check(lib.cst_bleu_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos, dev), out.data_ptr(),
                                   stats.data_ptr() if comps else None, bad.data_ptr() if bad is not None else None, dev.index,
                                   torch.cuda.current_stream(dev).cuda_stream))
         return (out, stats) if comps else out
@@ -137,7 +139,7 @@ class Rouge(_RowScorer):
         """ROUGE-L of token rows -> float64 CUDA tensor (n_total,); ``bad`` as in ``Bleu.bleu_rows``."""
         dev = self.device
         out = torch.empty(cand.shape[0] * (2 if greedy is not None else 1), dtype=torch.float64, device=dev)
-        check(lib.cst_rouge_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos), out.data_ptr(),
+        check(lib.cst_rouge_scores(*_row_args(cand, greedy, refs, cands_per_video, use_eos, dev), out.data_ptr(),
                                    bad.data_ptr() if bad is not None else None,
                                    dev.index, torch.cuda.current_stream(dev).cuda_stream))
         return out
