@@ -189,6 +189,7 @@ __device__ __forceinline__ void mt_video_refs(const RowsView& p, int64_t video, 
 
 // bleu_out [4][n_total] (order-major: row 3 is the BLEU-4 vector the reward reads), comps_out [n_total][6]
 // = testlen, reflen, correct[4] (what the corpus-level score adds up; guess[k] = max(testlen - k, 0)).
+template <int ESZ>
 __global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double* __restrict__ bleu_out,
                                                         int* __restrict__ comps_out) {
     constexpr u32 T = BL_TAB_SLOTS;
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double
                 for (u32 i = threadIdx.x; i < T; i += MT_THREADS) z[i] = make_uint4(0, 0, 0, 0);
             }
             const int n_try = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
-            mt_load_rows<BL_LOADS_FIRST != 0>(cbase, gbase, S, cb, n_try, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctok, sL, warp, lane);
+            mt_load_rows<BL_LOADS_FIRST != 0>(cbase, gbase, S, cb, n_try, p.pitch_c, ESZ ? ESZ : p.cand_esz, p.cand_width, p.use_eos, ctok, sL, warp, lane);
             __syncthreads();
             int nC, n_entC, Lh;
             {
@@ -254,7 +255,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double
             for (int64_t rb = r0; rb < r1;) {
                 const int left = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
                 mt_load_rows<BL_LOADS_FIRST != 0>(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, left,
-                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctok, sL, warp, lane);
+                             p.pitch_r, ESZ ? ESZ : p.ref_esz, p.ref_width, p.use_eos, ctok, sL, warp, lane);
                 __syncthreads();                     // (also: every candidate key is in the table, the list is free,
                                                      //  and the previous stage's finds are done with it)
                 int n_entR, nR;
@@ -356,6 +357,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_bleu(const RowsView p, double
 
 __device__ __forceinline__ u32 rg_home(u32 code, u32 C) { return __umulhi(code * 0x9E3779B1u, C); }
 
+template <int ESZ>
 __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, double* __restrict__ scores) {
     __shared__ __align__(16) u32 mask[RG_MASK_WORDS];
     __shared__ __align__(16) u32 dict[RG_DICT_MAX];
@@ -380,7 +382,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
 #pragma unroll 1
         for (int cb = 0; cb < n_local; cb += CST2_ROWS) {
             const int nC = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
-            mt_load_rows(cbase, gbase, S, cb, nC, p.pitch_c, p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
+            mt_load_rows(cbase, gbase, S, cb, nC, p.pitch_c, ESZ ? ESZ : p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
             if (threadIdx.x < CST2_ROWS) {
                 s_lcs[threadIdx.x] = 0;
                 s_key[threadIdx.x] = 0u;
@@ -397,7 +399,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                     d[threadIdx.x] = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
                 }
                 mt_load_rows(reinterpret_cast<const char*>(p.refs) + (size_t)rb * p.pitch_r, nullptr, 0x7fffffff, 0, left,
-                             p.pitch_r, p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
+                             p.pitch_r, ESZ ? ESZ : p.ref_esz, p.ref_width, p.use_eos, ctokR, sLr, warp, lane);
                 __syncthreads();
                 // how many of the loaded references this batch takes (every warp works it out for itself)
                 int nR;
@@ -584,10 +586,15 @@ extern "C" int cst_bleu_scores(const void* cand, const void* greedy, int32_t can
     if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_bleu_scores: cannot select device %d", device);
     static bool attr_set[64] = {false};
     if (device < 0 || device >= 64 || !attr_set[device]) {
-        CST_CUDA_TRY(cudaFuncSetAttribute(k_bleu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BL_SMEM));
+        CST_CUDA_TRY(cudaFuncSetAttribute(k_bleu<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BL_SMEM));
+        CST_CUDA_TRY(cudaFuncSetAttribute(k_bleu<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BL_SMEM));
         if (device >= 0 && device < 64) attr_set[device] = true;     // (a constant: racing threads set the same value)
     }
-    k_bleu<<<mt_grid(device, n_videos, 6), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
+    // (int32 rows on both sides -- what the callers of this package keep on the device -- get the element size compiled in)
+    if (p.cand_esz == 4 && p.ref_esz == 4)
+        k_bleu<4><<<mt_grid(device, n_videos, 6), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
+    else
+        k_bleu<0><<<mt_grid(device, n_videos, 6), MT_THREADS, BL_SMEM, (cudaStream_t)stream>>>(p, bleu_out, comps_out);
     cst_count_launch();
     CST_CUDA_TRY(cudaGetLastError());
     return CST_OK;
@@ -606,7 +613,10 @@ extern "C" int cst_rouge_scores(const void* cand, const void* greedy, int32_t ca
     if (!scores_out) return cst_fail(CST_E_ARG, "cst_rouge_scores: NULL output");
     CstDeviceGuard guard(device);
     if (!guard.ok) return cst_fail(CST_E_CUDA, "cst_rouge_scores: cannot select device %d", device);
-    k_rouge<<<mt_grid(device, n_videos, 6), MT_THREADS, 0, (cudaStream_t)stream>>>(p, scores_out);
+    if (p.cand_esz == 4 && p.ref_esz == 4)
+        k_rouge<4><<<mt_grid(device, n_videos, 6), MT_THREADS, 0, (cudaStream_t)stream>>>(p, scores_out);
+    else
+        k_rouge<0><<<mt_grid(device, n_videos, 6), MT_THREADS, 0, (cudaStream_t)stream>>>(p, scores_out);
     cst_count_launch();
     CST_CUDA_TRY(cudaGetLastError());
     return CST_OK;
