@@ -125,3 +125,39 @@ def test_config5_scb_star_4096_videos_properties_and_slice(world):
     want = ro.score_rows(list(b['sampled'][lo * 20:hi * 20].astype(np.int64)), gts, oracle, 1, 20, 1)
     scores = scorer.score_rows(c, RefSet.coerce(r, dev), 20, use_eos=1).cpu().numpy()
     _close64(scores[lo * 20:hi * 20], want)
+
+
+def test_other_scorers_4096_videos_properties_and_slice(world):
+    """BLEU-4 / ROUGE-L as the reward scorer (train.py:119-124) on the config-5 shape: properties over all
+    81,920 captions (scores in [0, 1]; a caption scored against references that contain it gets ROUGE-L 1
+    and BLEU-1..3 of 1 up to the scorer's 1e-9 offsets; SCB* rewards of a video sum to zero), and a slice of
+    64 videos held to the restated scorers."""
+    cst, dev, _, _, _ = world
+    from cst_captioning_b200 import synth
+    from cst_captioning_b200.reward import RefSet
+    from oracle import bleu_rouge_oracle as bo
+    from oracle import reward_oracle as ro
+    b = synth.make_batch(4096, 20, 20, seed=1000)
+    c, r = torch.from_numpy(b['sampled']).to(dev), torch.from_numpy(b['refs']).to(dev)
+    refset = RefSet.coerce(r, dev)
+    bleu, rouge = cst.Bleu(device=dev), cst.Rouge(device=dev)
+    lo, hi = 2000, 2064
+    gts = [b['refs'][v].astype(np.int64) for v in range(lo, hi)]
+    rows = list(b['sampled'][lo * 20:hi * 20].astype(np.int64))
+    for sc, theirs, exact in ((bleu, bo.Bleu(), False), (rouge, bo.Rouge(), True)):
+        s = sc.score_rows(c, refset, 20, use_eos=1)
+        assert float(s.min()) >= 0.0 and float(s.max()) <= 1.0 and bool(torch.isfinite(s).all())
+        want = ro.score_rows(rows, gts, theirs, 1, 20, 1)
+        got = s[lo * 20:hi * 20].cpu().numpy()
+        if exact:
+            np.testing.assert_array_equal(got, want)
+        else:
+            np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-300)
+        rew, m, bs = cst.get_cst_reward(c, r, sc, expand_feat=1, seq_per_img=20, scb_captions=20, scb_baseline=2, use_eos=1)
+        assert float(rew[:, 0].reshape(4096, 20).double().sum(1).abs().max()) < 1e-5
+        assert float(m) == pytest.approx(float(bs), rel=1e-12)
+    # every reference scored against its own video's references
+    own = r.reshape(4096 * 20, -1)
+    assert bool((rouge.score_rows(own, refset, 20, use_eos=1) == 1.0).all())
+    b123 = bleu.bleu_rows(own, refset, 20, use_eos=1)[:3]
+    assert float((b123 - 1.0).abs().max()) < 1e-8
