@@ -403,6 +403,7 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                 __syncthreads();
                 // how many of the loaded references this batch takes (every warp works it out for itself)
                 int nR;
+                bool any_long;
                 {
                     const int L = (lane < left) ? (sLr[lane] & 0xff) : 0;
                     int tok = (lane < left) ? (L > 0 ? L : 1) : 0;       // an empty sentence is ONE empty token
@@ -415,30 +416,36 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                     nR = __popc(__ballot_sync(CST_FULL, lane < left && (u32)tok * 5u <= 4u * RG_DICT_MAX &&
                                                             (u32)tok * 5u * (u32)(lane + 1) <= 4u * RG_MASK_WORDS));
                     if (nR < 1) nR = 1;                                  // (one row of 32 tokens always fits)
+                    any_long = __ballot_sync(CST_FULL, lane < nR && L > 16) != 0u;
                 }
                 const u32 C = min((u32)RG_DICT_MAX, (u32)RG_MASK_WORDS / (u32)nR);
                 if (warp == 0 && cb == 0 && lane < nR) bad_rows += (u32)(sLr[lane] >> 8);
                 if (warp == 1 && !cand_counted && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
                 cand_counted = true;
-                // ---- the references' tokens -> dictionary; position bit -> mask[slot][reference] ----
+                // ---- the references' tokens -> dictionary; position bit -> mask[slot][reference].  Half a warp
+                // per row (captions are mostly shorter than 16 tokens); rows beyond that get a second pass
+                // for their upper halves ----
 #pragma unroll 1
-                for (int t = (int)threadIdx.x; t < nR * 32; t += MT_THREADS) {
-                    const int r = t >> 5, j = t & 31;
-                    const int L = sLr[r] & 0xff;
-                    if (j < (L > 0 ? L : 1)) {
-                        const u32 code = L > 0 ? (u32)ctokR[r * CST2_TOK_STRIDE + j] : 0u;   // (0: the empty token)
-                        u32 idx = rg_home(code, C);
+                for (int half = 0; half < (any_long ? 2 : 1); ++half) {
 #pragma unroll 1
-                        for (;;) {
-                            const u32 cur = *reinterpret_cast<volatile u32*>(&dict[idx]);
-                            if (cur == code) break;
-                            if (cur == 0xffffffffu) {
-                                const u32 old = atomicCAS(&dict[idx], 0xffffffffu, code);
-                                if (old == 0xffffffffu || old == code) break;
+                    for (int t = (int)threadIdx.x; t < nR * 16; t += MT_THREADS) {
+                        const int r = t >> 4, j = (t & 15) + 16 * half;
+                        const int L = sLr[r] & 0xff;
+                        if (j < (L > 0 ? L : 1)) {
+                            const u32 code = L > 0 ? (u32)ctokR[r * CST2_TOK_STRIDE + j] : 0u;   // (0: the empty token)
+                            u32 idx = rg_home(code, C);
+#pragma unroll 1
+                            for (;;) {
+                                const u32 cur = *reinterpret_cast<volatile u32*>(&dict[idx]);
+                                if (cur == code) break;
+                                if (cur == 0xffffffffu) {
+                                    const u32 old = atomicCAS(&dict[idx], 0xffffffffu, code);
+                                    if (old == 0xffffffffu || old == code) break;
+                                }
+                                idx = (idx + 1u == C) ? 0u : idx + 1u;
                             }
-                            idx = (idx + 1u == C) ? 0u : idx + 1u;
+                            atomicOr(&mask[idx * (u32)nR + (u32)r], 1u << j);
                         }
-                        atomicOr(&mask[idx * (u32)nR + (u32)r], 1u << j);
                     }
                 }
                 __syncthreads();
@@ -480,7 +487,10 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                         const int Lr = sLr[lane] & 0xff;
                         const u32 lenr = (u32)(Lr > 0 ? Lr : 1);
                         lcs = (u32)__popc(~V & (lenr >= 32u ? 0xffffffffu : ((1u << lenr) - 1u)));
-                        key = (((lcs << 12) / lenr) << 12) | (lcs << 6) | lenr;
+                        // (the key only has to ORDER distinct fractions: they lie >= 4 apart on this scale, the fast
+                        //  float quotient is off by less than 1; equal fractions may get keys one apart, and either
+                        //  one's (lcs, len) gives the same double)
+                        key = ((u32)(__fdividef((float)(lcs << 12), (float)lenr)) << 12) | (lcs << 6) | lenr;
                     }
                     lcs = __reduce_max_sync(CST_FULL, lcs);
                     key = __reduce_max_sync(CST_FULL, key);
