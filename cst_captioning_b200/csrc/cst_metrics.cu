@@ -456,14 +456,14 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                 for (int h = warp; h < nC; h += MT_WARPS) {
                     const int Lh = sLc[h] & 0xff;
                     const int steps = Lh > 0 ? Lh : 1;
-                    u32 slot = RG_NONE;
+                    u32 off = RG_NONE;               // word offset of the token's row of masks, if any reference holds it
                     if (lane < steps) {
                         const u32 code = Lh > 0 ? (u32)ctokC[h * CST2_TOK_STRIDE + lane] : 0u;
                         u32 idx = rg_home(code, C);
 #pragma unroll 1
                         for (;;) {
                             const u32 cur = dict[idx];
-                            if (cur == code) { slot = idx; break; }
+                            if (cur == code) { off = idx * (u32)nR; break; }
                             if (cur == 0xffffffffu) break;
                             idx = (idx + 1u == C) ? 0u : idx + 1u;
                         }
@@ -471,13 +471,15 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                     const bool on = lane < nR;
                     const u32* mr = mask + lane;
                     u32 V = 0xffffffffu;
+                    // (a token no reference of the batch holds leaves V as it is: only the others are stepped through)
+                    u32 present = __ballot_sync(CST_FULL, off != RG_NONE);
 #pragma unroll 1
-                    for (int i = 0; i < steps; ++i) {
-                        const u32 d = __shfl_sync(CST_FULL, slot, i);
-                        if (d != RG_NONE) {          // (a token no reference of the batch holds leaves V as it is)
-                            const u32 U = on ? (V & mr[d * (u32)nR]) : 0u;
-                            V = (V + U) | (V - U);
-                        }
+                    while (present) {
+                        const int i = __ffs(present) - 1;
+                        present &= present - 1u;
+                        const u32 d = __shfl_sync(CST_FULL, off, i);
+                        const u32 U = on ? (V & mr[d]) : 0u;
+                        V = (V + U) | (V - U);
                     }
                     // prec = lcs / len(candidate): the largest lcs; rec = lcs / len(reference): fractions with
                     // denominators <= 32 differ by >= 2^-10, so floor(4096 lcs / len) orders them, and equal
