@@ -370,6 +370,10 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
     const int warp = __shfl_sync(CST_FULL, (int)(threadIdx.x >> 5), 0);
     const int S = p.cands_per_video;
     const int n_local = p.greedy ? 2 * S : S;
+    if (threadIdx.x < CST2_ROWS) {                   // (re-zeroed by their reader, warp 0)
+        s_lcs[threadIdx.x] = 0;
+        s_key[threadIdx.x] = 0u;
+    }
 
 #pragma unroll 1
     for (int64_t video = blockIdx.x; video < p.n_videos; video += gridDim.x) {
@@ -383,11 +387,8 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
         for (int cb = 0; cb < n_local; cb += CST2_ROWS) {
             const int nC = (n_local - cb) < CST2_ROWS ? (n_local - cb) : CST2_ROWS;
             mt_load_rows(cbase, gbase, S, cb, nC, p.pitch_c, ESZ ? ESZ : p.cand_esz, p.cand_width, p.use_eos, ctokC, sLc, warp, lane);
-            if (threadIdx.x < CST2_ROWS) {
-                s_lcs[threadIdx.x] = 0;
-                s_key[threadIdx.x] = 0u;
-            }
             bool cand_counted = false;
+            int Lc_mine = 0;                         // warp 0, lane h: L | bad << 8 of candidate row h (kept for the end)
 #pragma unroll 1
             for (int64_t rb = r0; rb < r1;) {
                 const int left = (int)((r1 - rb) < CST2_ROWS ? (r1 - rb) : CST2_ROWS);
@@ -420,7 +421,10 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                 }
                 const u32 C = min((u32)RG_DICT_MAX, (u32)RG_MASK_WORDS / (u32)nR);
                 if (warp == 0 && cb == 0 && lane < nR) bad_rows += (u32)(sLr[lane] >> 8);
-                if (warp == 1 && !cand_counted && lane < nC) bad_rows += (u32)(sLc[lane] >> 8);
+                if (warp == 0 && !cand_counted) {
+                    Lc_mine = lane < nC ? sLc[lane] : 0;
+                    bad_rows += (u32)(Lc_mine >> 8);
+                }
                 cand_counted = true;
                 // ---- the references' tokens -> dictionary; position bit -> mask[slot][reference].  Half a warp
                 // per row (captions are mostly shorter than 16 tokens); rows beyond that get a second pass
@@ -504,25 +508,34 @@ __global__ void __launch_bounds__(MT_THREADS, 6) k_rouge(const RowsView p, doubl
                 rb += nR;
                 __syncthreads();
             }
-            if (r0 >= r1) __syncthreads();
-            // Rouge.calc_score: F-measure of the two maxima, in the scorer's operation order
-            if (threadIdx.x < nC) {
-                const int h = (int)threadIdx.x;
-                const int c = cb + h;
-                const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
-                const int Lh = sLc[h] & 0xff;
-                if (r0 >= r1) bad_rows += (u32)(sLc[h] >> 8);
-                const double prec = (double)s_lcs[h] / (double)(Lh > 0 ? Lh : 1);
-                const u32 kbest = s_key[h];
-                const double rec = kbest ? (double)((kbest >> 6) & 63u) / (double)(kbest & 63u) : 0.0;
-                const double beta2 = 1.2 * 1.2;
-                double score = 0.0;
-                if (prec != 0.0 && rec != 0.0)
-                    score = __ddiv_rn(__dmul_rn(__dmul_rn(__dadd_rn(1.0, beta2), prec), rec),
-                                      __dadd_rn(rec, __dmul_rn(beta2, prec)));
-                scores[out] = score;
+            if (r0 >= r1) {                          // (no references: the candidates' lengths still have to land)
+                __syncthreads();
+                if (warp == 0) {
+                    Lc_mine = lane < nC ? sLc[lane] : 0;
+                    bad_rows += (u32)(Lc_mine >> 8);
+                }
             }
-            __syncthreads();
+            // Rouge.calc_score: F-measure of the two maxima, in the scorer's operation order.  Warp 0 alone;
+            // the others go on to the next batch (nothing they touch before its first barrier is read here).
+            if (warp == 0) {
+                const int lbest = s_lcs[lane];
+                const u32 kbest = s_key[lane];
+                s_lcs[lane] = 0;
+                s_key[lane] = 0u;
+                if (lane < nC) {
+                    const int c = cb + lane;
+                    const int64_t out = (c >= S) ? p.n_cand + video * S + (c - S) : video * S + c;
+                    const int Lh = Lc_mine & 0xff;
+                    const double prec = (double)lbest / (double)(Lh > 0 ? Lh : 1);
+                    const double rec = kbest ? (double)((kbest >> 6) & 63u) / (double)(kbest & 63u) : 0.0;
+                    const double beta2 = 1.2 * 1.2;
+                    double score = 0.0;
+                    if (prec != 0.0 && rec != 0.0)
+                        score = __ddiv_rn(__dmul_rn(__dmul_rn(__dadd_rn(1.0, beta2), prec), rec),
+                                          __dadd_rn(rec, __dmul_rn(beta2, prec)));
+                    scores[out] = score;
+                }
+            }
         }
         if (bad_rows && p.bad_out) atomicAdd(p.bad_out, bad_rows);
     }
